@@ -1,0 +1,55 @@
+# Build of the B200-native solver. Same verbs as the reference makefile (makefile:1-15:
+# build / clean / run / runOn2) but: optimised host code, explicit sm_100a device code with
+# line info, no MPI, no hard-coded CUDA 11.0 path.
+CUDA_HOME ?= /usr/local/cuda
+NVCC      ?= $(CUDA_HOME)/bin/nvcc
+CXX       ?= g++
+PKG       := mpi_openmp_cuda_b200
+LIBDIR    := $(PKG)/_lib
+GENCODE   := -gencode arch=compute_100a,code=sm_100a
+CXXFLAGS  := -O3 -std=c++17 -fPIC -Wall -Wextra -Iinclude -pthread
+NVCCFLAGS := -O3 -std=c++17 $(GENCODE) -lineinfo -Iinclude -Xcompiler -fPIC -Xptxas -v
+INPUT     ?= data/input1.txt
+GPUS      ?= 1
+
+CORE_SRC := csrc/core/problem.cpp csrc/core/oracle.cpp csrc/core/plan.cpp
+CUDA_SRC := csrc/cuda/align_kernel.cu
+CORE_LIB := $(LIBDIR)/libseqalign_core.so
+CUDA_LIB := $(LIBDIR)/libseqalign_cuda.so
+
+.PHONY: build core cuda clean run runOn2 test sass
+
+build: core cuda final
+
+core: $(CORE_LIB)
+cuda: $(CUDA_LIB)
+
+$(CORE_LIB): $(CORE_SRC) csrc/core/core.hpp include/seqalign.h
+	@mkdir -p $(LIBDIR)
+	$(CXX) $(CXXFLAGS) -shared -o $@ $(CORE_SRC)
+
+$(CUDA_LIB): $(CUDA_SRC) $(wildcard csrc/cuda/*.cuh) include/seqalign.h $(CORE_LIB)
+	@mkdir -p $(LIBDIR)
+	$(NVCC) $(NVCCFLAGS) -shared -o $@ $(CUDA_SRC) -L$(LIBDIR) -lseqalign_core -Xlinker -rpath -Xlinker '$$ORIGIN'
+
+# `final` keeps the reference's binary name and stdin->stdout contract (makefile:4,11).
+final: csrc/host/final_main.cpp $(CORE_LIB) $(CUDA_LIB)
+	$(CXX) $(CXXFLAGS) -o $@ csrc/host/final_main.cpp -L$(LIBDIR) -lseqalign_core -ldl \
+	    -Wl,-rpath,'$$ORIGIN/$(LIBDIR)'
+
+clean:
+	rm -f final $(LIBDIR)/*.so csrc/**/*.o
+
+run: build
+	./final --gpus $(GPUS) < $(INPUT)
+
+# The reference's runOn2 target spreads 2 ranks over 2 hosts (makefile:15); a single
+# 8xB200 box is the deployment unit here, so the analogue is 2 GPUs of one node.
+runOn2: build
+	./final --gpus 2 < $(INPUT)
+
+test: build
+	python -m pytest tests -x -q -m "not gpu"
+
+sass: cuda
+	$(CUDA_HOME)/bin/cuobjdump -sass $(CUDA_LIB) > profiles/align_kernel.sass

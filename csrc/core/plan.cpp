@@ -1,0 +1,379 @@
+// Planner + packer + CPU blob executor.
+//
+// What this replaces in the reference:
+//   * main.c:110-121,184-185 — static "rows = N / P, remainder on root" split. Here the unit
+//     of work is a (sequence, offset-tile) item whose cost is its padded cell count; whole
+//     sequences (or, when sequences are scarce, single tiles) are dealt to the least-loaded
+//     GPU, costliest first.
+//   * cudaFunctions.cu:35-61 — four separate constant-memory uploads. Here weights, pair
+//     table, Seq1, the per-sequence descriptors, the item list and every Seq2 are packed into
+//     ONE blob: one H2D copy on a single GPU, one in-kernel broadcast on several.
+//
+// Algorithm the tiling serves: with V[i][j] = value(seq2[i], seq1[j]) and
+// P_n[k] = sum_{i<k} V[i][i+n],
+//     score(n,0) = P_n[m]                       (no gap)
+//     score(n,k) = P_{n+1}[m] + (P_n[k] - P_{n+1}[k])   for 1 <= k < m
+// so per offset n the best k is a running max of the prefix difference of two neighbouring
+// diagonals — O(len1*len2) instead of the reference's O(len1*len2^2).
+#include <algorithm>
+#include <climits>
+#include <cstdlib>
+#include <cstring>
+#include <numeric>
+
+#include "core.hpp"
+
+static_assert(sizeof(sa_blob_header) == 256, "blob header must be 256 bytes");
+static_assert(sizeof(sa_seq_desc) == 16, "seq desc must be 16 bytes");
+static_assert(sizeof(sa_item) == 8, "item must be 8 bytes");
+
+namespace sa {
+namespace {
+
+constexpr uint32_t kR = SA_DIAG_PER_LANE;
+constexpr uint32_t kWarpDiag = SA_DIAG_PER_WARP;
+constexpr uint32_t kWarps = SA_CTA_WARPS;
+constexpr uint32_t kU = SA_ROW_UNROLL;
+constexpr int32_t kNeg = -(1 << 30);  // "minus infinity" that survives one addition
+
+inline uint32_t round_up(uint32_t v, uint32_t m) { return (v + m - 1) / m * m; }
+
+struct SeqPlan {
+    uint32_t len = 0;
+    int32_t ndiag = 0;
+    uint32_t ntiles = 0;
+    uint32_t wd_log2 = 0;
+    uint32_t crow = kU;
+    uint64_t item_cost = 0;  // padded cells per tile
+    uint32_t rows_padded() const { return crow * (kWarps >> wd_log2); }
+};
+
+SeqPlan plan_sequence(uint32_t len1, uint32_t len2) {
+    SeqPlan sp;
+    sp.len = len2;
+    sp.ndiag = (int32_t)len1 - (int32_t)len2;
+    if (sp.ndiag < 0) {  // no candidates (cudaFunctions.cu:116 loop never runs)
+        sp.ntiles = 0;
+        return sp;
+    }
+    const uint32_t d = sp.ndiag == 0 ? 1u : (uint32_t)sp.ndiag;  // offsets to score
+    uint64_t best_cost = ~0ull;
+    for (uint32_t l = 0; (1u << l) <= kWarps; ++l) {
+        const uint32_t wd = 1u << l, wr = kWarps / wd;
+        const uint32_t crow = round_up((len2 + wr - 1) / wr, kU);
+        const uint32_t tn = kWarpDiag * wd;
+        const uint32_t ntiles = (d + tn - 1) / tn;
+        const uint64_t cost = (uint64_t)ntiles * tn * wr * crow;
+        if (cost < best_cost) {
+            best_cost = cost;
+            sp.wd_log2 = l;
+            sp.crow = crow;
+            sp.ntiles = ntiles;
+            sp.item_cost = (uint64_t)tn * wr * crow;
+        }
+    }
+    return sp;
+}
+
+inline uint64_t pack_key(int32_t score, uint32_t n) {
+    return ((uint64_t)((uint32_t)score ^ 0x80000000u) << 32) | (uint64_t)(0xFFFFFFFFu - n);
+}
+
+}  // namespace
+}  // namespace sa
+
+extern "C" {
+
+int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, size_t* blob_bytes) {
+    using namespace sa;
+    if (!p || !blob_bytes || world < 1 || world > SA_MAX_WORLD) {
+        set_error("sa_plan_pack: bad argument");
+        return SA_ERR_ARG;
+    }
+    const uint32_t len1 = (uint32_t)p->seq1.size();
+    const uint32_t nseq = (uint32_t)p->seq2.size();
+    if (p->seq1.size() > SA_GPU_MAX_SEQ1) {
+        set_error("Seq1 longer than the GPU executor supports");
+        return SA_ERR_UNSUPPORTED;
+    }
+    int64_t maxw = 0;
+    for (int i = 0; i < 4; ++i) maxw = std::max<int64_t>(maxw, std::llabs((int64_t)p->weights[i]));
+    const Alphabet al = build_alphabet(*p);
+    if (!al.ok) {
+        set_error("more than five distinct non-letter bytes in the input");
+        return SA_ERR_UNSUPPORTED;
+    }
+    std::vector<SeqPlan> plans(nseq);
+    uint32_t max_rows = kU;
+    uint64_t total_cells = 0, padded_cells = 0, nitems64 = 0;
+    for (uint32_t s = 0; s < nseq; ++s) {
+        const size_t l2 = p->seq2[s].size();
+        if (l2 > SA_GPU_MAX_SEQ2) {
+            set_error("a Seq2 is longer than the GPU executor supports");
+            return SA_ERR_UNSUPPORTED;
+        }
+        // every partial sum must stay inside +-2^29 so that kNeg + sum never wraps
+        if (maxw * (int64_t)(l2 + 256) * 4 >= (1ll << 31)) {
+            set_error("weights too large for the int32 GPU path");
+            return SA_ERR_UNSUPPORTED;
+        }
+        plans[s] = plan_sequence(len1, (uint32_t)l2);
+        max_rows = std::max(max_rows, plans[s].rows_padded());
+        total_cells += (uint64_t)sa_problem_candidates(p, (int32_t)s);
+        padded_cells += plans[s].item_cost * plans[s].ntiles;
+        nitems64 += plans[s].ntiles;
+    }
+    if (nitems64 > 0x7FFFFFFFull) {
+        set_error("too many work items");
+        return SA_ERR_UNSUPPORTED;
+    }
+    const uint32_t nitems = (uint32_t)nitems64;
+
+    // ---- layout
+    const uint32_t len1_padded = round_up(len1 + SA_SEQ1_TAIL_PAD, 16);
+    uint64_t off = sizeof(sa_blob_header);
+    const uint32_t off_lut = (uint32_t)off;
+    off += sizeof(int32_t) * SA_ALPHABET * SA_ALPHABET;
+    const uint32_t off_seq1 = (uint32_t)off;
+    off += len1_padded;
+    const uint32_t off_seqtab = (uint32_t)off;
+    off += (uint64_t)sizeof(sa_seq_desc) * nseq;
+    off = (off + 15) / 16 * 16;
+    const uint32_t off_items = (uint32_t)off;
+    off += (uint64_t)sizeof(sa_item) * nitems;
+    off = (off + 15) / 16 * 16;
+    const uint32_t off_seq2 = (uint32_t)off;
+    std::vector<uint32_t> seq_off(nseq);
+    for (uint32_t s = 0; s < nseq; ++s) {
+        seq_off[s] = (uint32_t)off;
+        off += round_up(std::max(plans[s].rows_padded(), (uint32_t)p->seq2[s].size()), 16);
+        if (off >= 0xFFFFF000ull) {
+            set_error("blob larger than 4 GiB");
+            return SA_ERR_UNSUPPORTED;
+        }
+    }
+    const size_t total = (size_t)off;
+    *blob_bytes = total;
+    if (!dst) return SA_OK;
+    if (cap < total) {
+        set_error("sa_plan_pack_into: destination too small");
+        return SA_ERR_ARG;
+    }
+
+    // ---- partition: deal sequences (or tiles, when sequences are scarce) to ranks
+    std::vector<uint32_t> order(nseq);
+    std::iota(order.begin(), order.end(), 0u);
+    std::stable_sort(order.begin(), order.end(),
+                     [&](uint32_t a, uint32_t b) { return plans[a].item_cost > plans[b].item_cost; });
+    struct RankItem {
+        uint32_t seq, tile;
+    };
+    std::vector<std::vector<RankItem>> per_rank((size_t)world);
+    std::vector<uint64_t> load((size_t)world, 0);
+    std::vector<uint8_t> home(nseq, 0);
+    const bool by_tile = world > 1 && nseq < 2u * (uint32_t)world;
+    auto lightest = [&]() { return (int)(std::min_element(load.begin(), load.end()) - load.begin()); };
+    for (uint32_t s : order) {
+        const SeqPlan& sp = plans[s];
+        if (sp.ntiles == 0) continue;
+        if (!by_tile) {
+            const int r = lightest();
+            home[s] = (uint8_t)r;
+            for (uint32_t t = 0; t < sp.ntiles; ++t) per_rank[(size_t)r].push_back({s, t});
+            load[(size_t)r] += sp.item_cost * sp.ntiles;
+        } else {
+            for (uint32_t t = 0; t < sp.ntiles; ++t) {
+                const int r = lightest();
+                if (t == 0) home[s] = (uint8_t)r;
+                per_rank[(size_t)r].push_back({s, t});
+                load[(size_t)r] += sp.item_cost;
+            }
+        }
+    }
+
+    // ---- fill
+    unsigned char* base = static_cast<unsigned char*>(dst);
+    std::memset(base, 0, total);
+    sa_blob_header* h = reinterpret_cast<sa_blob_header*>(base);
+    h->magic = SA_BLOB_MAGIC;
+    h->version = SA_BLOB_VERSION;
+    h->total_bytes = (uint32_t)total;
+    h->flags = 0;
+    std::memcpy(h->weights, p->weights, sizeof(h->weights));
+    h->len1 = len1;
+    h->len1_padded = len1_padded;
+    h->nseq = nseq;
+    h->nitems = nitems;
+    h->off_lut = off_lut;
+    h->off_seq1 = off_seq1;
+    h->off_seqtab = off_seqtab;
+    h->off_items = off_items;
+    h->off_seq2 = off_seq2;
+    h->max_rows_padded = max_rows;
+    h->chunk_bytes = 1u << 16;
+    h->nchunks = (uint32_t)((total + h->chunk_bytes - 1) / h->chunk_bytes);
+    h->total_cells = total_cells;
+    h->padded_cells = padded_cells;
+    h->world = (uint32_t)world;
+    build_lut(al, p->weights, reinterpret_cast<int32_t*>(base + off_lut));
+    for (uint32_t j = 0; j < len1; ++j) base[off_seq1 + j] = (unsigned char)(al.code[(unsigned char)p->seq1[j]] * 4);
+    sa_seq_desc* tab = reinterpret_cast<sa_seq_desc*>(base + off_seqtab);
+    for (uint32_t s = 0; s < nseq; ++s) {
+        const SeqPlan& sp = plans[s];
+        tab[s].off = seq_off[s];
+        tab[s].len = (uint16_t)sp.len;
+        tab[s].ndiag = sp.ndiag;
+        tab[s].ntiles = (uint16_t)sp.ntiles;
+        tab[s].wd_log2 = (uint8_t)sp.wd_log2;
+        tab[s].home = home[s];
+        tab[s].crow = (uint16_t)sp.crow;
+        const std::string& q = p->seq2[s];
+        for (size_t i = 0; i < q.size(); ++i) base[seq_off[s] + i] = (unsigned char)al.code[(unsigned char)q[i]];
+    }
+    sa_item* items = reinterpret_cast<sa_item*>(base + off_items);
+    uint32_t w = 0;
+    for (int r = 0; r < world; ++r) {
+        h->rank_first_item[r] = w;
+        for (const RankItem& it : per_rank[(size_t)r]) items[w++] = sa_item{it.seq, it.tile};
+    }
+    for (int r = world; r <= SA_MAX_WORLD; ++r) h->rank_first_item[r] = w;
+    return SA_OK;
+}
+
+int sa_plan_pack(const sa_problem* p, int world, void** blob, size_t* blob_bytes) {
+    if (!blob || !blob_bytes) {
+        sa::set_error("sa_plan_pack: null argument");
+        return SA_ERR_ARG;
+    }
+    size_t need = 0;
+    int rc = sa_plan_pack_into(p, world, nullptr, 0, &need);
+    if (rc != SA_OK) return rc;
+    void* mem = nullptr;
+    if (posix_memalign(&mem, 256, need ? need : 256) != 0) return SA_ERR_NOMEM;
+    rc = sa_plan_pack_into(p, world, mem, need, blob_bytes);
+    if (rc != SA_OK) {
+        std::free(mem);
+        return rc;
+    }
+    *blob = mem;
+    return SA_OK;
+}
+
+void sa_blob_free(void* blob) { std::free(blob); }
+
+// CPU walk of the blob with the kernel's exact decomposition (see align_kernel.cu):
+// per item, 16 "warps" = wd offset groups x wr row chunks; per lane R+1 running prefixes and R
+// running maxima; per-chunk results combined in row order; best (score, smallest n) folded
+// into a packed 64-bit key; when the last tile of a sequence lands, the winning diagonal is
+// rescanned for the first k.
+int sa_blob_execute_cpu(const void* blob, size_t blob_bytes, int32_t* out4) {
+    using namespace sa;
+    if (!blob || !out4 || blob_bytes < sizeof(sa_blob_header)) {
+        set_error("sa_blob_execute_cpu: bad argument");
+        return SA_ERR_ARG;
+    }
+    const unsigned char* base = static_cast<const unsigned char*>(blob);
+    const sa_blob_header* h = reinterpret_cast<const sa_blob_header*>(base);
+    if (h->magic != SA_BLOB_MAGIC || h->version != SA_BLOB_VERSION || h->total_bytes > blob_bytes) {
+        set_error("sa_blob_execute_cpu: not a blob of this version");
+        return SA_ERR_ARG;
+    }
+    const int32_t* lut = reinterpret_cast<const int32_t*>(base + h->off_lut);
+    const unsigned char* seq1 = base + h->off_seq1;
+    const sa_seq_desc* tab = reinterpret_cast<const sa_seq_desc*>(base + h->off_seqtab);
+    const sa_item* items = reinterpret_cast<const sa_item*>(base + h->off_items);
+    std::vector<uint64_t> key(h->nseq, 0);
+    std::vector<uint32_t> cnt(h->nseq, 0);
+    auto value = [&](unsigned code2, unsigned c4) { return lut[code2 * SA_ALPHABET + (c4 >> 2)]; };
+
+    for (uint32_t s = 0; s < h->nseq; ++s)
+        if (tab[s].ntiles == 0) {
+            out4[4 * s] = INT_MIN;
+            out4[4 * s + 1] = out4[4 * s + 2] = out4[4 * s + 3] = 0;
+        }
+
+    std::vector<int32_t> csum((size_t)kWarps * (kR + 1) * 32), cmax((size_t)kWarps * kR * 32);
+    for (uint32_t it = 0; it < h->nitems; ++it) {
+        const uint32_t s = items[it].seq, tile = items[it].tile;
+        const sa_seq_desc& sd = tab[s];
+        const unsigned char* s2 = base + sd.off;
+        const uint32_t wd = 1u << sd.wd_log2, wr = kWarps / wd, crow = sd.crow;
+        const uint32_t tn = kWarpDiag * wd, n0 = tile * tn;
+        if ((uint64_t)n0 + wr * crow + tn > h->len1_padded) {
+            set_error("sa_blob_execute_cpu: window outside padded Seq1");
+            return SA_ERR_ARG;
+        }
+        for (uint32_t w = 0; w < kWarps; ++w) {
+            const uint32_t g = w & (wd - 1), q = w >> sd.wd_log2;
+            for (uint32_t lane = 0; lane < 32; ++lane) {
+                const uint32_t d0 = g * kWarpDiag + lane * kR;
+                int32_t P[kR + 1], best[kR];
+                for (uint32_t r = 0; r <= kR; ++r) P[r] = 0;
+                for (uint32_t r = 0; r < kR; ++r) best[r] = kNeg;
+                for (uint32_t i = q * crow; i < (q + 1) * crow; ++i) {
+                    const unsigned code2 = s2[i];
+                    for (uint32_t r = 0; r <= kR; ++r) P[r] += value(code2, seq1[n0 + i + d0 + r]);
+                    for (uint32_t r = 0; r < kR; ++r) best[r] = std::max(best[r], P[r] - P[r + 1]);
+                }
+                for (uint32_t r = 0; r <= kR; ++r) csum[((size_t)w * (kR + 1) + r) * 32 + lane] = P[r];
+                for (uint32_t r = 0; r < kR; ++r) cmax[((size_t)w * kR + r) * 32 + lane] = best[r];
+            }
+        }
+        uint64_t tile_key = 0;
+        for (uint32_t d = 0; d < tn; ++d) {
+            const uint32_t g = d / kWarpDiag, lane = (d % kWarpDiag) / kR, r = d % kR;
+            int32_t A = 0, T0 = 0, T1 = 0, M = kNeg;
+            for (uint32_t q = 0; q < wr; ++q) {
+                const uint32_t w = q * wd + g;
+                const int32_t s0 = csum[((size_t)w * (kR + 1) + r) * 32 + lane];
+                const int32_t s1 = csum[((size_t)w * (kR + 1) + r + 1) * 32 + lane];
+                const int32_t mx = cmax[((size_t)w * kR + r) * 32 + lane];
+                M = std::max(M, A + mx);
+                A += s0 - s1;
+                T0 += s0;
+                T1 += s1;
+            }
+            const uint32_t n = n0 + d;
+            if (sd.ndiag == 0) {
+                if (n == 0) tile_key = std::max(tile_key, pack_key(T0, 0));
+            } else if (n < (uint32_t)sd.ndiag) {
+                tile_key = std::max(tile_key, pack_key(T1 + M, n));
+            }
+        }
+        key[s] = std::max(key[s], tile_key);
+        if (++cnt[s] == sd.ntiles) {
+            const int32_t best = (int32_t)((uint32_t)(key[s] >> 32) ^ 0x80000000u);
+            const uint32_t n = 0xFFFFFFFFu - (uint32_t)(key[s] & 0xFFFFFFFFu);
+            int32_t k = 0;
+            if (sd.ndiag != 0) {
+                int32_t T0 = 0, T1 = 0;
+                for (uint32_t i = 0; i < sd.len; ++i) {
+                    T0 += value(s2[i], seq1[n + i]);
+                    T1 += value(s2[i], seq1[n + i + 1]);
+                }
+                if (T0 != best) {
+                    int32_t S = 0;
+                    k = -1;
+                    for (uint32_t i = 0; i + 1 < sd.len; ++i) {
+                        S += value(s2[i], seq1[n + i]) - value(s2[i], seq1[n + i + 1]);
+                        if (T1 + S == best) {
+                            k = (int32_t)(i + 1);
+                            break;
+                        }
+                    }
+                    if (k < 0) {
+                        set_error("sa_blob_execute_cpu: winning diagonal does not reproduce the best score");
+                        return SA_ERR_ARG;
+                    }
+                }
+            }
+            out4[4 * s] = best;
+            out4[4 * s + 1] = (int32_t)n;
+            out4[4 * s + 2] = k;
+            out4[4 * s + 3] = 0;
+        }
+    }
+    return SA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,210 @@
+/*
+ * seqalign.h — C ABI of the B200-native exhaustive sequence-alignment solver.
+ *
+ * The problem solved is the one the reference course project solves with
+ * MPI + OpenMP + CUDA (reference: main.c:46-244, cudaFunctions.cu:63-176):
+ * given weights w1..w4, a long sequence Seq1 and N shorter sequences Seq2_i,
+ * find for every Seq2_i the offset n and single-gap ("mutant") position k that
+ * maximise  w1*#identical - w2*#conservative - w3*#semi-conservative - w4*#other.
+ *
+ * Layers exposed here (all `extern "C"`, usable from C, C++, ctypes):
+ *   1. parsing / formatting   (reference: main.c:76-108, main.c:199-211)
+ *   2. pair-value table        (reference: main.c:14-44, main.c:59-60)
+ *   3. CPU oracle              (race-free restatement of cudaFunctions.cu:63-176)
+ *   4. planner + packer        (reference: main.c:110-121 work split; cudaFunctions.cu:35-61 uploads)
+ *   5. GPU executor            (reference: cudaFunctions.cu:178-242 + kernel :63-176)
+ *
+ * Everything in 1-4 lives in libseqalign_core.so (no CUDA dependency);
+ * 5 lives in libseqalign_cuda.so (sm_100a only).
+ */
+#ifndef SEQALIGN_H_
+#define SEQALIGN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ limits */
+
+/* Buffer caps of the reference (myProto.h:3-4). Inputs inside these caps are
+ * guaranteed to take the GPU path; the parser itself accepts longer tokens. */
+#define SA_REF_MAX_SEQ1 2999
+#define SA_REF_MAX_SEQ2 1999
+
+/* Hard limits of the GPU executor (longer inputs fall back to the CPU oracle). */
+#define SA_GPU_MAX_SEQ1 (1u << 20)
+#define SA_GPU_MAX_SEQ2 8192u
+
+/* Alphabet: code 0 = padding (scores 0 against everything), 1..26 = 'A'..'Z',
+ * 27..31 = up to five distinct non-letter bytes seen in the input. */
+#define SA_ALPHABET 32
+
+/* ------------------------------------------------------------- error codes */
+
+enum sa_status {
+    SA_OK = 0,
+    SA_ERR_PARSE = 1,       /* malformed input (missing tokens, bad integers) */
+    SA_ERR_ARG = 2,         /* bad argument */
+    SA_ERR_UNSUPPORTED = 3, /* input outside the GPU executor's limits */
+    SA_ERR_CUDA = 4,        /* a CUDA runtime call failed (see sa_last_error) */
+    SA_ERR_NOMEM = 5,
+    SA_ERR_TOO_LARGE = 6    /* exceeds a fixed-capacity entry point's maximum */
+};
+
+/* Thread-local human-readable description of the last failure. */
+const char* sa_last_error(void);
+/* Used by the sibling libraries to report through the same channel. */
+void sa_set_last_error(const char* msg);
+
+/* ----------------------------------------------------------------- problem */
+
+typedef struct sa_problem sa_problem;
+
+/* Parse the reference's stdin grammar (main.c:76-108): whitespace-separated
+ * tokens `w1 w2 w3 w4  Seq1  N  Seq2_0 .. Seq2_{N-1}`; ASCII a-z are
+ * upper-cased; CRLF, repeated blanks and a missing final newline are fine.
+ * Missing tokens are an error (the reference reads garbage there). */
+int sa_parse(const char* text, size_t len, sa_problem** out);
+
+/* Build a problem from already-tokenised parts (sequences are upper-cased). */
+int sa_problem_create(const int32_t weights[4], const char* seq1, size_t len1,
+                      int32_t nseq, const char* const* seq2, const size_t* len2,
+                      sa_problem** out);
+void sa_problem_free(sa_problem* p);
+
+int32_t sa_problem_nseq(const sa_problem* p);
+void sa_problem_weights(const sa_problem* p, int32_t w[4]);
+size_t sa_problem_len1(const sa_problem* p);
+const char* sa_problem_seq1(const sa_problem* p);
+size_t sa_problem_len2(const sa_problem* p, int32_t i);
+const char* sa_problem_seq2(const sa_problem* p, int32_t i);
+/* Number of (n,k) candidates of sequence i: (len1-len2)*len2, 1 if the lengths
+ * are equal, 0 if len2 > len1 (cudaFunctions.cu:74,116-118). */
+int64_t sa_problem_candidates(const sa_problem* p, int32_t i);
+int64_t sa_problem_total_candidates(const sa_problem* p);
+/* Serialise back to the input grammar (used by the synthetic generator). */
+size_t sa_problem_serialize(const sa_problem* p, char* buf, size_t cap);
+
+/* --------------------------------------------------------------- pair table */
+
+/* class(a,b) for two raw (upper-cased) bytes: 0 identical, 1 same type-1
+ * group, 2 same type-2 group, 3 otherwise (main.c:59-60; cudaFunctions.cu:134-141). */
+int sa_pair_class(unsigned char a, unsigned char b);
+
+/* ------------------------------------------------------------------- oracle */
+
+/* Result triple per sequence: out[3*i+0] = score, +1 = n, +2 = k.
+ * `sa_solve_cpu_naive` is the literal O(len1*len2^2) restatement of the
+ * reference kernel's intended semantics; `sa_solve_cpu_fast` is an independent
+ * O(len1*len2) formulation; `threads` <= 0 means hardware concurrency. */
+int sa_solve_cpu_naive(const sa_problem* p, int32_t* out, int threads);
+int sa_solve_cpu_fast(const sa_problem* p, int32_t* out, int threads);
+
+/* ---------------------------------------------------------------- formatter */
+
+/* `#i: score: S, n: N, k: K\n` per sequence (main.c:204,209). Returns the number
+ * of bytes needed (excluding NUL); writes at most cap bytes. */
+size_t sa_format(const int32_t* results, int32_t nseq, char* buf, size_t cap);
+
+/* ------------------------------------------------------------ planner/packer */
+
+/* Static geometry shared by the packer and the kernel. */
+#define SA_CTA_THREADS 512        /* 16 warps per CTA                          */
+#define SA_CTA_WARPS 16
+#define SA_DIAG_PER_LANE 8        /* R: consecutive offsets per thread          */
+#define SA_DIAG_PER_WARP 256      /* 32 * R                                     */
+#define SA_ROW_UNROLL 8           /* U: rows per inner-loop trip                */
+#define SA_BLOB_MAGIC 0x31424153u /* "SAB1" */
+#define SA_BLOB_VERSION 2u
+#define SA_SEQ1_TAIL_PAD 4608u    /* zero bytes after Seq1 so every window is in range */
+
+#define SA_MAX_WORLD 16
+
+typedef struct sa_blob_header {
+    uint32_t magic, version, total_bytes, flags;
+    int32_t weights[4];
+    uint32_t len1, len1_padded, nseq, nitems;
+    uint32_t off_lut;    /* int32[32*32]: value(seq2 code a, seq1 code b) at a*32+b */
+    uint32_t off_seq1;   /* uint8[len1_padded]: code*4 (pre-scaled LUT byte offset) */
+    uint32_t off_seqtab; /* sa_seq_desc[nseq]                                       */
+    uint32_t off_items;  /* sa_item[nitems], grouped by rank, costliest first       */
+    uint32_t off_seq2;   /* uint8 codes, each sequence 16-byte aligned, zero padded */
+    uint32_t max_rows_padded;
+    uint32_t chunk_bytes; /* fabric broadcast granularity */
+    uint32_t nchunks;
+    uint64_t total_cells;  /* sum over sequences of candidates                 */
+    uint64_t padded_cells; /* cells the tiling actually evaluates              */
+    uint32_t world;        /* number of GPUs the item list is partitioned for  */
+    uint32_t rank_first_item[SA_MAX_WORLD + 1]; /* rank r owns items [r], [r+1]) */
+    uint32_t reserved[22];
+} sa_blob_header; /* 256 bytes */
+
+typedef struct sa_seq_desc {
+    uint32_t off;      /* byte offset of the sequence's codes inside the blob  */
+    uint16_t len;      /* len2 (<= SA_GPU_MAX_SEQ2)                            */
+    uint16_t crow;     /* rows per warp chunk (multiple of SA_ROW_UNROLL)      */
+    int32_t ndiag;     /* len1-len2 ; 0 = equal length ; <0 = no candidates    */
+    uint16_t ntiles;   /* items of this sequence                               */
+    uint8_t wd_log2;   /* log2(warps laid across offsets); rows get 16>>wd_log2 */
+    uint8_t home;      /* rank holding this sequence's key + arrival counter   */
+} sa_seq_desc; /* 16 bytes */
+
+typedef struct sa_item {
+    uint32_t seq;
+    uint32_t tile;
+} sa_item;
+
+/* Plan (choose per-sequence tiling, order items by cost) and pack everything
+ * the GPU needs into ONE contiguous blob (one H2D copy / one fabric broadcast).
+ * `*blob` is malloc'ed; free with sa_blob_free. Returns SA_ERR_UNSUPPORTED when
+ * the input is outside the GPU executor's limits. */
+int sa_plan_pack(const sa_problem* p, int world, void** blob, size_t* blob_bytes);
+/* Same, into caller memory (e.g. pinned): returns needed size in *blob_bytes
+ * (call with dst == NULL to size the buffer). */
+int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, size_t* blob_bytes);
+void sa_blob_free(void* blob);
+
+/* CPU executor of a packed blob: walks the item list with exactly the tile /
+ * row-chunk / combine / packed-key / first-k logic of the GPU kernel. Used to
+ * validate planner+packer without a GPU (out: int32[4*nseq] = score,n,k,0). */
+int sa_blob_execute_cpu(const void* blob, size_t blob_bytes, int32_t* out4);
+
+/* The work partition over `world` GPUs (new-build analogue of main.c:110-121) is part
+ * of the plan: whole sequences are dealt to the least-loaded rank, costliest first;
+ * when there are fewer than 2*world sequences the deal happens per tile instead, so a
+ * single long sequence still spreads over all GPUs. */
+
+/* ------------------------------------------------------------- GPU executor */
+
+/* Bytes of device scratch needed for a blob with `nseq` sequences
+ * (packed argmax keys, per-sequence arrival counters, control words). */
+size_t sa_cuda_scratch_bytes(uint32_t nseq);
+
+/* Zero a freshly allocated scratch area (the kernel leaves it zeroed again). */
+int sa_cuda_scratch_init(void* d_scratch, size_t bytes, void* stream);
+
+/* Solve a packed blob that already sits in device memory.
+ *   d_blob     device pointer to the blob (16-byte aligned)
+ *   d_out      device int32[4*nseq]: score, n, k, 0 per sequence
+ *   d_scratch  device scratch of sa_cuda_scratch_bytes(nseq), zeroed once
+ *   nseq/nitems as in the blob header (host copies; no D2H needed to launch)
+ *   stream     cudaStream_t (NULL = default stream)
+ * One kernel launch, no allocation, no synchronisation.
+ * Replaces cudaFunctions.cu:178-242 (per-row malloc+launch+sync) and :63-176. */
+int sa_cuda_solve_blob(const void* d_blob, int32_t* d_out, void* d_scratch,
+                       uint32_t nseq, uint32_t nitems, void* stream);
+
+/* Convenience: plan+pack `p`, upload, solve, download (allocates; synchronous).
+ * out: int32[3*nseq]. */
+int sa_cuda_solve_problem(const sa_problem* p, int32_t* out, int device);
+
+/* Number of kernel launches issued by this library in this process. */
+uint64_t sa_cuda_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SEQALIGN_H_ */

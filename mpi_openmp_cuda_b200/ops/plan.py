@@ -1,0 +1,79 @@
+"""Planner + packer: one contiguous blob per problem (reference: main.c:110-121 split,
+cudaFunctions.cu:35-61 + :189-201 uploads)."""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _native as N
+
+
+@dataclass
+class PackedBlob:
+    """Host-side packed problem. `data` is a uint8 array (numpy, or a pinned torch tensor
+    when `pinned=True` was requested) holding exactly `nbytes` valid bytes."""
+
+    data: object
+    nbytes: int
+    header: N.BlobHeader
+
+    @property
+    def nseq(self) -> int:
+        return int(self.header.nseq)
+
+    @property
+    def nitems(self) -> int:
+        return int(self.header.nitems)
+
+    def numpy(self) -> np.ndarray:
+        d = self.data
+        return d if isinstance(d, np.ndarray) else d.numpy()
+
+    def seq_table(self) -> np.ndarray:
+        raw = self.numpy()[self.header.off_seqtab : self.header.off_seqtab + 16 * self.nseq]
+        dt = np.dtype([("off", "<u4"), ("len", "<u2"), ("crow", "<u2"), ("ndiag", "<i4"),
+                       ("ntiles", "<u2"), ("wd_log2", "u1"), ("home", "u1")])
+        return raw.view(dt)
+
+    def items(self) -> np.ndarray:
+        raw = self.numpy()[self.header.off_items : self.header.off_items + 8 * self.nitems]
+        return raw.view(np.dtype([("seq", "<u4"), ("tile", "<u4")]))
+
+
+def blob_size(problem, world: int = 1) -> int:
+    need = C.c_size_t()
+    N.check(N.core().sa_plan_pack_into(problem.handle, world, None, 0, C.byref(need)))
+    return int(need.value)
+
+
+def plan_pack(problem, world: int = 1, pinned: bool = False, out=None) -> PackedBlob:
+    """Plan the tiling, partition over `world` GPUs and pack. Raises NativeError with
+    code SA_ERR_UNSUPPORTED when the input is outside the GPU executor's limits."""
+    need = blob_size(problem, world)
+    if out is not None:
+        buf = out
+        if buf.numel() < need:
+            raise ValueError("provided buffer too small")
+        ptr = buf.data_ptr()
+    elif pinned:
+        import torch
+
+        buf = torch.empty(need, dtype=torch.uint8, pin_memory=True)
+        ptr = buf.data_ptr()
+    else:
+        buf = np.empty(need, dtype=np.uint8)
+        ptr = buf.ctypes.data
+    got = C.c_size_t()
+    N.check(N.core().sa_plan_pack_into(problem.handle, world, C.c_void_p(ptr), need, C.byref(got)))
+    hdr = N.BlobHeader.from_buffer_copy(C.string_at(ptr, C.sizeof(N.BlobHeader)))
+    return PackedBlob(buf, int(got.value), hdr)
+
+
+def execute_blob_cpu(blob: PackedBlob) -> np.ndarray:
+    """Walk the blob on the CPU with the GPU kernel's tile logic -> int32[nseq, 3]."""
+    arr = blob.numpy()
+    out = np.zeros((max(blob.nseq, 1), 4), dtype=np.int32)
+    N.check(N.core().sa_blob_execute_cpu(C.c_void_p(arr.ctypes.data), blob.nbytes, out.ctypes.data_as(C.POINTER(C.c_int32))))
+    return out[: blob.nseq, :3].copy()
