@@ -1,0 +1,219 @@
+#!/usr/bin/env python
+"""Headline benchmark (BASELINE.json): solve time per input, device-timed, max over ranks,
+and candidates/s — for this framework (`--impl ours`, default) and for the unmodified reference
+build (`--impl reference`, see baseline/).
+
+A "step" is one complete solve of the configured input (all N sequences): the analogue of the
+reference's whole `mpiexec -np P ./final < input` run after start-up.
+
+Prints ONE JSON line on rank 0 (see the task contract for the keys).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
+    ap.add_argument("--input", default="input3.txt", help="shipped input under data/ (BASELINE.json configs)")
+    ap.add_argument("--scale", type=int, default=1,
+                    help="replicate the input's sequences SCALE x per GPU (weak scaling: total = SCALE*gpus)")
+    ap.add_argument("--synthetic", type=int, default=1024,
+                    help="also report the synthetic N-scaled config (x input3 per GPU; 0 = skip)")
+    return ap.parse_args()
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def build_problem(args, n_gpus):
+    from mpi_openmp_cuda_b200 import Problem
+    from mpi_openmp_cuda_b200.models.synthetic import scaled_input3
+
+    path = ROOT / "data" / args.input
+    total_scale = args.scale * n_gpus
+    if total_scale == 1:
+        return Problem.from_file(path)
+    return scaled_input3(total_scale, path, seed=1)
+
+
+def time_ours_single(problem, steps, warmup, device="cuda:0"):
+    """Kernel-only (device-timed, resident blob) and end-to-end (pack + H2D + kernel + D2H)."""
+    import torch
+
+    from mpi_openmp_cuda_b200.models.alignment import AlignmentSolver
+    from mpi_openmp_cuda_b200.ops.score import launch_count
+    from mpi_openmp_cuda_b200.utils.clocks import ClockSampler
+    from mpi_openmp_cuda_b200.utils.timing import L2Flusher
+
+    torch.cuda.set_device(device)
+    solver = AlignmentSolver(device)
+    flusher = L2Flusher(device)
+    blob = solver.pack(problem)
+    res = solver.solve_packed(blob).copy()
+    # -- kernel only: blob resident, events around the single launch, L2 flushed between steps
+    for _ in range(warmup):
+        flusher.flush()
+        solver.exec.run(blob.header)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(torch.cuda.current_device()).start()
+    launches0 = launch_count()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    torch.cuda.synchronize()
+    t_wall0 = time.perf_counter()
+    for e0, e1 in ev:
+        flusher.flush()
+        e0.record()
+        solver.exec.run(blob.header)
+        e1.record()
+    torch.cuda.synchronize()
+    t_wall = time.perf_counter() - t_wall0
+    kernel_ms = [a.elapsed_time(b) for a, b in ev]
+    launches = launch_count() - launches0
+    # -- end to end through the public API: pack into pinned memory, H2D, kernel, D2H, sync
+    for _ in range(warmup):
+        solver.solve(problem)
+    e2e_ms = []
+    for _ in range(steps):
+        flusher.flush()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = solver.solve(problem)  # includes the final stream synchronize
+        e1.record()
+        e1.synchronize()
+        e2e_ms.append(e0.elapsed_time(e1))
+    # -- end to end with the problem already packed in pinned memory (H2D + kernel + D2H only)
+    pre_ms = []
+    for _ in range(steps):
+        flusher.flush()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        solver.solve_packed(blob)
+        e1.record()
+        e1.synchronize()
+        pre_ms.append(e0.elapsed_time(e1))
+    clocks = sampler.stop()
+    import numpy as np
+
+    assert np.array_equal(out, res)
+    return {
+        "kernel_ms": kernel_ms, "e2e_ms": e2e_ms, "e2e_prepacked_ms": pre_ms, "launches": launches,
+        "clocks": clocks, "h2d": blob.nbytes, "d2h": blob.nseq * 16, "result": res,
+        "padded_cells": int(blob.header.padded_cells), "nitems": blob.nitems, "wall_s": t_wall,
+    }
+
+
+def run_ours(args):
+    rank, world, local = dist_env()
+    n_gpus = args.gpus
+    import torch
+
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "no CUDA device; bench.py needs a B200"}))
+        return 1
+    problem = build_problem(args, n_gpus)
+    cands = problem.candidates()
+    if n_gpus > 1 or world > 1:
+        from mpi_openmp_cuda_b200.parallel.dist_bench import time_ours_distributed
+
+        m = time_ours_distributed(problem, args.steps, args.warmup)
+        if m is None:  # non-zero ranks print nothing
+            return 0
+    else:
+        m = time_ours_single(problem, args.steps, args.warmup)
+    # correctness gate: a fast wrong answer is not a benchmark
+    from mpi_openmp_cuda_b200.ops.oracle import solve_cpu
+    import numpy as np
+
+    if problem.nseq <= 4096:
+        assert np.array_equal(m["result"], solve_cpu(problem, "fast")), "GPU result differs from the CPU oracle"
+    ms = statistics.fmean(m["kernel_ms"])
+    e2e = statistics.fmean(m["e2e_ms"])
+    pre = statistics.fmean(m["e2e_prepacked_ms"])
+    line = {
+        "metric": "candidates/s (one full solve of the input; device-timed, max over ranks)",
+        "value": cands / (ms * 1e-3),
+        "unit": "candidates/s",
+        "n_gpus": n_gpus,
+        "steps": args.steps,
+        "warmup": args.warmup,
+        "ms_per_step": ms,
+        "higher_is_better": True,
+        "scaling": "weak",
+        "vs_baseline": None,
+        "dtype": "int32 (exact integer scores; the reference is int32 too)",
+        "data": f"shipped reference input data/{args.input}" + ("" if args.scale * n_gpus == 1 else
+                f" replicated x{args.scale * n_gpus} with random substitutions (synthetic)"),
+        "impl": "ours",
+        "config": {
+            "model": "exhaustive (n,k) alignment search",
+            "input": args.input, "scale_per_gpu": args.scale, "nseq": problem.nseq,
+            "len1": len(problem.seq1), "candidates": cands, "global_batch": problem.nseq,
+            "seq_len": len(problem.seq1), "parallelism": f"dp{n_gpus}",
+            "l2": "flushed between timed steps (256 MiB fill)",
+            "padded_cells": m["padded_cells"], "items": m["nitems"],
+        },
+        "solve_ms_min": min(m["kernel_ms"]),
+        "e2e": {"value": cands / (e2e * 1e-3), "unit": "candidates/s", "ms_per_step": e2e,
+                "what": "solver.solve(problem): plan+pack into pinned memory, H2D, kernel, D2H, sync",
+                "h2d_bytes_per_step": m["h2d"], "d2h_bytes_per_step": m["d2h"],
+                "prepacked_ms_per_step": pre},
+        "gpu_launches": m["launches"],
+        "clocks": m["clocks"],
+    }
+    if args.synthetic and n_gpus == 1:
+        line["synthetic"] = synthetic_report(args)
+    print(json.dumps(line))
+    return 0
+
+
+def synthetic_report(args):
+    """BASELINE.json configs[3]: N-scaled input3 (compute-bound); kernel-only + roofline inputs."""
+    from mpi_openmp_cuda_b200.models.synthetic import scaled_input3
+
+    p = scaled_input3(args.synthetic, ROOT / "data" / "input3.txt", seed=1)
+    m = time_ours_single(p, max(3, min(args.steps, 10)), 3)
+    ms = statistics.fmean(m["kernel_ms"])
+    return {"config": f"input3 x{args.synthetic} ({p.nseq} sequences)", "candidates": p.candidates(),
+            "kernel_ms": ms, "candidates_per_s": p.candidates() / (ms * 1e-3),
+            "padded_cells_per_s": m["padded_cells"] / (ms * 1e-3),
+            "e2e_ms": statistics.fmean(m["e2e_ms"]), "e2e_prepacked_ms": statistics.fmean(m["e2e_prepacked_ms"]),
+            "h2d_bytes": m["h2d"]}
+
+
+def run_reference(args):
+    rank, world, local = dist_env()
+    try:
+        from baseline.run_ref import bench_reference
+    except Exception as e:  # harness missing
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": f"baseline harness import failed: {e}"}))
+        return 0
+    out = bench_reference(args, rank, world)
+    if rank == 0 and out is not None:
+        print(json.dumps(out))
+    return 0
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    sys.exit(run_reference(a) if a.impl == "reference" else run_ours(a))

@@ -104,7 +104,7 @@ int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, siz
         return SA_ERR_UNSUPPORTED;
     }
     std::vector<SeqPlan> plans(nseq);
-    uint32_t max_rows = kU;
+    uint32_t max_rows = kU, max_window = 16;
     uint64_t total_cells = 0, padded_cells = 0, nitems64 = 0;
     for (uint32_t s = 0; s < nseq; ++s) {
         const size_t l2 = p->seq2[s].size();
@@ -119,6 +119,8 @@ int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, siz
         }
         plans[s] = plan_sequence(len1, (uint32_t)l2);
         max_rows = std::max(max_rows, plans[s].rows_padded());
+        if (plans[s].ntiles)
+            max_window = std::max(max_window, round_up(plans[s].rows_padded() + (kWarpDiag << plans[s].wd_log2), 16));
         total_cells += (uint64_t)sa_problem_candidates(p, (int32_t)s);
         padded_cells += plans[s].item_cost * plans[s].ntiles;
         nitems64 += plans[s].ntiles;
@@ -210,6 +212,7 @@ int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, siz
     h->off_items = off_items;
     h->off_seq2 = off_seq2;
     h->max_rows_padded = max_rows;
+    h->max_window_bytes = max_window;
     h->chunk_bytes = 1u << 16;
     h->nchunks = (uint32_t)((total + h->chunk_bytes - 1) / h->chunk_bytes);
     h->total_cells = total_cells;

@@ -1,0 +1,492 @@
+// sm_100a scoring kernel + host launch path.
+//
+// Replaces, in the reference:
+//   * cudaFunctions.cu:63-176  `calc_result` — one thread per Seq2 letter, the (n,k) double loop
+//     inside the kernel with 3 block barriers and 2 levels of atomics per candidate;
+//   * cudaFunctions.cu:178-242 — per-row cudaMalloc + cudaGetDeviceProperties + launch +
+//     cudaDeviceSynchronize;
+//   * cudaFunctions.cu:9-13,35-61 — five __constant__ symbols filled by separate copies.
+//
+// Design (not a port): ONE persistent launch per problem. A work item is (sequence,
+// offset tile). Each thread owns R=8 consecutive offsets n and walks rows i, keeping the
+// running prefixes P_n[k] of 9 neighbouring diagonals and the running maxima of
+// P_n[k]-P_{n+1}[k] in registers (score(n,k) = P_{n+1}[m] + P_n[k] - P_{n+1}[k], see plan.cpp).
+// The 16 warps of a CTA split an item as wd offset groups x wr row chunks; chunk results
+// are merged in row order through shared memory, folded into one packed 64-bit
+// (score, ~n) key per tile and atomicMax'ed into the sequence's slot. The CTA that delivers a
+// sequence's last tile rescans the winning diagonal for the first k and writes the result.
+// Inputs are staged with TMA bulk copies (cp.async.bulk + mbarrier); the pair-value table
+// sits in shared memory with one bank per letter, so the per-cell lookup is conflict free.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <climits>
+#include <cstdint>
+#include <cstdio>
+#include <mutex>
+#include <string>
+
+#include "seqalign.h"
+
+namespace {
+
+constexpr int kThreads = SA_CTA_THREADS;
+constexpr int kWarps = SA_CTA_WARPS;
+constexpr int kR = SA_DIAG_PER_LANE;
+constexpr int kU = SA_ROW_UNROLL;
+constexpr int kNeg = -(1 << 30);
+constexpr uint32_t kLutBytes = SA_ALPHABET * SA_ALPHABET * 4;
+constexpr uint32_t kSumWords = kWarps * (kR + 1) * 32;
+constexpr uint32_t kMaxWords = kWarps * kR * 32;
+static_assert(kR == 8 && kU == 8, "the inner loop is written for R = U = 8");
+
+struct KParams {
+    const unsigned char* blob;  // packed problem (sa_plan_pack)
+    int4* out;                  // (score, n, k, 0) per sequence
+    unsigned long long* key;    // packed argmax key per sequence, zero between launches
+    unsigned int* cnt;          // tiles delivered per sequence, zero between launches
+    unsigned int* ctrl;         // [0] next item, [1] CTAs finished; zero between launches
+    uint32_t item_begin, item_end;
+    uint32_t s2_cap, win_cap;   // shared-memory capacities (bytes, multiples of 16)
+    uint32_t write_empty;       // 1: this launch writes the rows of candidate-free sequences
+};
+
+// ------------------------------------------------------------------ PTX helpers
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+// TMA bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP).
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+
+__device__ __forceinline__ unsigned long long pack_key(int score, uint32_t n) {
+    return ((unsigned long long)((uint32_t)score ^ 0x80000000u) << 32) | (unsigned long long)(0xFFFFFFFFu - n);
+}
+__device__ __forceinline__ unsigned long long umax64(unsigned long long a, unsigned long long b) {
+    return a > b ? a : b;
+}
+__device__ __forceinline__ uint32_t byte_of(uint32_t lo, uint32_t hi, int k) {  // k in 0..7, compile time
+    return ((k < 4 ? lo : hi) >> (8 * (k & 3))) & 0xFFu;
+}
+
+// ------------------------------------------------------------------ the kernel
+
+__global__ void __launch_bounds__(kThreads, 2) sa_score_kernel(const KParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    unsigned char* const lut_b = smem;
+    unsigned char* const s2 = lut_b + kLutBytes;
+    unsigned char* const win = s2 + p.s2_cap;
+    int* const csum = reinterpret_cast<int*>(win + p.win_cap);
+    int* const cmax = csum + kSumWords;
+    unsigned long long* const red = reinterpret_cast<unsigned long long*>(cmax + kMaxWords);  // [kWarps]
+    unsigned long long* const mbar = red + kWarps;
+    int* const scan = reinterpret_cast<int*>(mbar + 1);  // [kWarps]
+    uint32_t* const ctl = reinterpret_cast<uint32_t*>(scan + kWarps);  // [0] item, [1] last flag, [2] first k
+
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
+    const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + hdr->off_seqtab);
+    const sa_item* const items = reinterpret_cast<const sa_item*>(p.blob + hdr->off_items);
+    const unsigned char* const seq1g = p.blob + hdr->off_seq1;
+    const uint32_t bar = smem_u32(mbar);
+    uint32_t parity = 0;
+
+    // Sequences longer than Seq1 have no candidates: (INT_MIN, 0, 0) as the reference's
+    // untouched `max` (cudaFunctions.cu:113,170-172).
+    if (p.write_empty) {
+        for (uint32_t s = blockIdx.x * kThreads + tid; s < hdr->nseq; s += gridDim.x * kThreads)
+            if (seqtab[s].ntiles == 0) p.out[s] = make_int4(INT_MIN, 0, 0, 0);
+    }
+
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    // Pair-value table -> shared memory, once per CTA.
+    if (tid == 0) {
+        mbar_expect_tx(bar, kLutBytes);
+        bulk_g2s(smem_u32(lut_b), p.blob + hdr->off_lut, kLutBytes, bar);
+    }
+    mbar_wait(bar, parity);
+    parity ^= 1u;
+
+    for (;;) {
+        if (tid == 0) ctl[0] = p.item_begin + atomicAdd(&p.ctrl[0], 1u);
+        __syncthreads();  // also: every read of s2/win/csum of the previous item is done
+        const uint32_t item = ctl[0];
+        if (item >= p.item_end) break;
+
+        const uint32_t seq = items[item].seq, tile = items[item].tile;
+        const sa_seq_desc sd = seqtab[seq];
+        const uint32_t wd_log2 = sd.wd_log2, wd = 1u << wd_log2, wr = (uint32_t)kWarps >> wd_log2;
+        const uint32_t crow = sd.crow, rows_padded = crow * wr;
+        const uint32_t tn = (uint32_t)SA_DIAG_PER_WARP << wd_log2, n0 = tile * tn;
+
+        if (tid == 0) {
+            const uint32_t s2_bytes = (rows_padded + 15u) & ~15u;
+            const uint32_t win_bytes = (rows_padded + tn + 15u) & ~15u;
+            mbar_expect_tx(bar, s2_bytes + win_bytes);
+            bulk_g2s(smem_u32(s2), p.blob + sd.off, s2_bytes, bar);
+            bulk_g2s(smem_u32(win), seq1g + n0, win_bytes, bar);
+        }
+        mbar_wait(bar, parity);
+        parity ^= 1u;
+
+        // ---- scan: this warp = offset group g, row chunk q
+        {
+            const uint32_t g = warp & (wd - 1u), q = warp >> wd_log2;
+            const uint32_t d0 = g * SA_DIAG_PER_WARP + lane * kR;
+            const unsigned char* wp = win + d0 + q * crow;  // letters of column (row + d0 + k)
+            const unsigned char* sp = s2 + q * crow;
+            int P[kR + 1], best[kR];
+#pragma unroll
+            for (int r = 0; r <= kR; ++r) P[r] = 0;
+#pragma unroll
+            for (int r = 0; r < kR; ++r) best[r] = kNeg;
+            uint2 lw0 = *reinterpret_cast<const uint2*>(wp);
+            for (uint32_t row = 0; row < crow; row += kU) {
+                const uint2 lw1 = *reinterpret_cast<const uint2*>(wp + row + kU);
+                const uint2 sc = *reinterpret_cast<const uint2*>(sp + row);
+                uint32_t L[2 * kU];
+#pragma unroll
+                for (int k = 0; k < kU; ++k) {
+                    L[k] = byte_of(lw0.x, lw0.y, k);
+                    L[kU + k] = byte_of(lw1.x, lw1.y, k);
+                }
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    const unsigned char* lrow = lut_b + byte_of(sc.x, sc.y, u) * (SA_ALPHABET * 4u);
+                    int v[kR + 1];
+#pragma unroll
+                    for (int r = 0; r <= kR; ++r) v[r] = *reinterpret_cast<const int*>(lrow + L[u + r]);
+#pragma unroll
+                    for (int r = 0; r <= kR; ++r) P[r] += v[r];
+#pragma unroll
+                    for (int r = 0; r < kR; ++r) best[r] = max(best[r], P[r] - P[r + 1]);
+                }
+                lw0 = lw1;
+            }
+#pragma unroll
+            for (int r = 0; r <= kR; ++r) csum[(warp * (kR + 1) + r) * 32 + lane] = P[r];
+#pragma unroll
+            for (int r = 0; r < kR; ++r) cmax[(warp * kR + r) * 32 + lane] = best[r];
+        }
+        __syncthreads();
+
+        // ---- merge row chunks in order, score every offset of the tile, keep the best
+        unsigned long long mykey = 0ull;
+        for (uint32_t t = tid; t < tn; t += kThreads) {
+            const uint32_t l = t & 31u, r = (t >> 5) & 7u, g = t >> 8;
+            int A = 0, T0 = 0, T1 = 0, M = kNeg;
+            for (uint32_t q = 0; q < wr; ++q) {
+                const uint32_t w = (q << wd_log2) + g;
+                const int s0 = csum[(w * (kR + 1) + r) * 32 + l];
+                const int s1 = csum[(w * (kR + 1) + r + 1) * 32 + l];
+                const int mx = cmax[(w * kR + r) * 32 + l];
+                M = max(M, A + mx);
+                A += s0 - s1;
+                T0 += s0;
+                T1 += s1;
+            }
+            const uint32_t n = n0 + g * SA_DIAG_PER_WARP + l * kR + r;
+            if (sd.ndiag == 0) {
+                if (n == 0) mykey = pack_key(T0, 0u);  // equal lengths: one candidate (cudaFunctions.cu:74-106)
+            } else if (n < (uint32_t)sd.ndiag) {
+                mykey = umax64(mykey, pack_key(T1 + M, n));
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mykey = umax64(mykey, __shfl_xor_sync(0xFFFFFFFFu, mykey, o));
+        if (lane == 0) red[warp] = mykey;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned long long v = lane < (uint32_t)kWarps ? red[lane] : 0ull;
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) v = umax64(v, __shfl_xor_sync(0xFFFFFFFFu, v, o));
+            if (lane == 0) {
+                atomicMax(&p.key[seq], v);
+                __threadfence();
+                const unsigned int old = atomicAdd(&p.cnt[seq], 1u);
+                ctl[1] = (old + 1u == sd.ntiles) ? 1u : 0u;
+                ctl[2] = 0x7FFFFFFFu;
+            }
+        }
+        __syncthreads();
+
+        // ---- last tile of this sequence: find the first k on the winning diagonal
+        if (ctl[1]) {
+            if (tid == 0) {
+                __threadfence();
+                red[0] = atomicMax(&p.key[seq], 0ull);  // coherent read of the final key
+            }
+            __syncthreads();
+            const unsigned long long fk = red[0];
+            const int bestv = (int)((uint32_t)(fk >> 32) ^ 0x80000000u);
+            const uint32_t nwin = 0xFFFFFFFFu - (uint32_t)(fk & 0xFFFFFFFFull);
+            int kres = 0;
+            if (sd.ndiag != 0) {
+                const int* lut_i = reinterpret_cast<const int*>(lut_b);
+                const uint32_t m = sd.len;
+                const uint32_t per = (m + kThreads - 1) / kThreads;
+                const uint32_t i0 = min(tid * per, m), i1 = min(i0 + per, m);
+                const unsigned char* c1 = seq1g + nwin;
+                int da = 0, sb = 0;
+                for (uint32_t i = i0; i < i1; ++i) {
+                    const int* lrow = lut_i + (uint32_t)s2[i] * SA_ALPHABET;
+                    const int a = lrow[c1[i] >> 2], b = lrow[c1[i + 1] >> 2];
+                    da += a - b;
+                    sb += b;
+                }
+                // block-wide exclusive scan of da, block sums of da and sb
+                int inc = da, tsb = sb;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int x = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+                    if (lane >= (uint32_t)o) inc += x;
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) tsb += __shfl_xor_sync(0xFFFFFFFFu, tsb, o);
+                if (lane == 31) scan[warp] = inc;
+                if (lane == 0) csum[warp] = tsb;
+                __syncthreads();
+                int before = 0, tot_da = 0, T1 = 0;
+#pragma unroll
+                for (int w = 0; w < kWarps; ++w) {
+                    const int x = scan[w];
+                    if ((uint32_t)w < warp) before += x;
+                    tot_da += x;
+                    T1 += csum[w];
+                }
+                const int T0 = T1 + tot_da;
+                if (T0 != bestv) {  // otherwise k = 0 wins the tie (checked first, cudaFunctions.cu:118,161)
+                    int S = before + inc - da;
+                    for (uint32_t i = i0; i < i1; ++i) {
+                        const int* lrow = lut_i + (uint32_t)s2[i] * SA_ALPHABET;
+                        S += lrow[c1[i] >> 2] - lrow[c1[i + 1] >> 2];
+                        if (i + 1 < m && T1 + S == bestv) {
+                            atomicMin(&ctl[2], i + 1u);
+                            break;
+                        }
+                    }
+                    __syncthreads();
+                    kres = (int)ctl[2];
+                }
+            }
+            if (tid == 0) {
+                p.out[seq] = make_int4(bestv, (int)nwin, kres, 0);
+                p.key[seq] = 0ull;  // leave the scratch zeroed for the next launch
+                p.cnt[seq] = 0u;
+            }
+        }
+    }
+
+    // Last CTA out re-arms the work queue for the next launch.
+    if (tid == 0) {
+        __threadfence();
+        const unsigned int done = atomicAdd(&p.ctrl[1], 1u);
+        if (done + 1u == gridDim.x) {
+            p.ctrl[0] = 0u;
+            p.ctrl[1] = 0u;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ host side
+
+std::atomic<uint64_t> g_launches{0};
+
+struct DeviceInfo {
+    bool ready = false;
+    int sm_count = 0;
+    int max_optin_smem = 0;
+    int smem_set = 0;
+};
+std::mutex g_mu;
+DeviceInfo g_dev[64];
+
+int fail(cudaError_t e, const char* what) {
+    std::string msg = std::string(what) + ": " + cudaGetErrorString(e);
+    sa_set_last_error(msg.c_str());
+    return SA_ERR_CUDA;
+}
+
+#define SA_CUDA_TRY(expr)                                  \
+    do {                                                   \
+        cudaError_t e__ = (expr);                          \
+        if (e__ != cudaSuccess) return fail(e__, #expr);   \
+    } while (0)
+
+inline size_t round_up_sz(size_t v, size_t m) { return (v + m - 1) / m * m; }
+
+size_t key_bytes(uint32_t nseq) { return round_up_sz((size_t)nseq * 8, 256); }
+size_t cnt_bytes(uint32_t nseq) { return round_up_sz((size_t)nseq * 4, 256); }
+
+uint32_t smem_bytes_for(uint32_t s2_cap, uint32_t win_cap) {
+    return kLutBytes + s2_cap + win_cap + (kSumWords + kMaxWords) * 4 + kWarps * 8 + 8 + kWarps * 4 + 16;
+}
+
+int device_info(int dev, DeviceInfo** out) {
+    if (dev < 0 || dev >= 64) {
+        sa_set_last_error("device index out of range");
+        return SA_ERR_ARG;
+    }
+    std::lock_guard<std::mutex> lock(g_mu);
+    DeviceInfo& d = g_dev[dev];
+    if (!d.ready) {
+        SA_CUDA_TRY(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev));
+        SA_CUDA_TRY(cudaDeviceGetAttribute(&d.max_optin_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+        d.ready = true;
+    }
+    *out = &d;
+    return SA_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t sa_cuda_scratch_bytes(uint32_t nseq) { return key_bytes(nseq) + cnt_bytes(nseq) + 256; }
+
+int sa_cuda_scratch_init(void* d_scratch, size_t bytes, void* stream) {
+    SA_CUDA_TRY(cudaMemsetAsync(d_scratch, 0, bytes, static_cast<cudaStream_t>(stream)));
+    return SA_OK;
+}
+
+int sa_cuda_solve_blob(const void* d_blob, const sa_blob_header* h, int32_t* d_out, void* d_scratch, void* stream) {
+    if (!d_blob || !h || !d_out || !d_scratch) {
+        sa_set_last_error("sa_cuda_solve_blob: null argument");
+        return SA_ERR_ARG;
+    }
+    if (h->magic != SA_BLOB_MAGIC || h->version != SA_BLOB_VERSION) {
+        sa_set_last_error("sa_cuda_solve_blob: header is not a blob of this version");
+        return SA_ERR_ARG;
+    }
+    if (h->nseq == 0) return SA_OK;
+    int dev = 0;
+    SA_CUDA_TRY(cudaGetDevice(&dev));
+    DeviceInfo* di = nullptr;
+    int rc = device_info(dev, &di);
+    if (rc != SA_OK) return rc;
+
+    KParams p;
+    p.blob = static_cast<const unsigned char*>(d_blob);
+    p.out = reinterpret_cast<int4*>(d_out);
+    unsigned char* sc = static_cast<unsigned char*>(d_scratch);
+    p.key = reinterpret_cast<unsigned long long*>(sc);
+    p.cnt = reinterpret_cast<unsigned int*>(sc + key_bytes(h->nseq));
+    p.ctrl = reinterpret_cast<unsigned int*>(sc + key_bytes(h->nseq) + cnt_bytes(h->nseq));
+    p.item_begin = 0;
+    p.item_end = h->nitems;
+    p.s2_cap = (h->max_rows_padded + 15u) & ~15u;
+    p.win_cap = (h->max_window_bytes + 15u) & ~15u;
+    p.write_empty = 1;
+    const uint32_t smem = smem_bytes_for(p.s2_cap, p.win_cap);
+    if ((int)smem > di->max_optin_smem) {
+        sa_set_last_error("sa_cuda_solve_blob: problem needs more shared memory than the device has");
+        return SA_ERR_UNSUPPORTED;
+    }
+    {
+        std::lock_guard<std::mutex> lock(g_mu);
+        if ((int)smem > di->smem_set) {
+            SA_CUDA_TRY(cudaFuncSetAttribute(sa_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            di->smem_set = (int)smem;
+        }
+    }
+    uint32_t grid = (uint32_t)di->sm_count * 2u;
+    if (h->nitems < grid) grid = h->nitems ? h->nitems : 1u;
+    sa_score_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+    SA_CUDA_TRY(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return SA_OK;
+}
+
+int sa_cuda_solve_problem(const sa_problem* prob, int32_t* out, int device) {
+    if (!prob || !out) {
+        sa_set_last_error("sa_cuda_solve_problem: null argument");
+        return SA_ERR_ARG;
+    }
+    void* blob = nullptr;
+    size_t bytes = 0;
+    int rc = sa_plan_pack(prob, 1, &blob, &bytes);
+    if (rc != SA_OK) return rc;
+    const sa_blob_header* h = static_cast<const sa_blob_header*>(blob);
+    const uint32_t nseq = h->nseq;
+    if (nseq == 0) {
+        sa_blob_free(blob);
+        return SA_OK;
+    }
+    void *d_blob = nullptr, *d_out = nullptr, *d_scratch = nullptr;
+    int4* h_out = nullptr;
+    auto cleanup = [&]() {
+        cudaFree(d_blob);
+        cudaFree(d_out);
+        cudaFree(d_scratch);
+        free(h_out);
+        sa_blob_free(blob);
+    };
+    cudaError_t e;
+#define SA_TRY_CLEAN(expr)                  \
+    do {                                    \
+        e = (expr);                         \
+        if (e != cudaSuccess) {             \
+            cleanup();                      \
+            return fail(e, #expr);          \
+        }                                   \
+    } while (0)
+    SA_TRY_CLEAN(cudaSetDevice(device));
+    const size_t scratch = sa_cuda_scratch_bytes(nseq);
+    SA_TRY_CLEAN(cudaMalloc(&d_blob, bytes));
+    SA_TRY_CLEAN(cudaMalloc(&d_out, (size_t)nseq * 16));
+    SA_TRY_CLEAN(cudaMalloc(&d_scratch, scratch));
+    SA_TRY_CLEAN(cudaMemcpy(d_blob, blob, bytes, cudaMemcpyHostToDevice));
+    SA_TRY_CLEAN(cudaMemset(d_scratch, 0, scratch));
+    rc = sa_cuda_solve_blob(d_blob, h, static_cast<int32_t*>(d_out), d_scratch, nullptr);
+    if (rc != SA_OK) {
+        cleanup();
+        return rc;
+    }
+    h_out = static_cast<int4*>(malloc((size_t)nseq * 16));
+    if (!h_out) {
+        cleanup();
+        return SA_ERR_NOMEM;
+    }
+    SA_TRY_CLEAN(cudaMemcpy(h_out, d_out, (size_t)nseq * 16, cudaMemcpyDeviceToHost));
+#undef SA_TRY_CLEAN
+    for (uint32_t s = 0; s < nseq; ++s) {
+        out[3 * s] = h_out[s].x;
+        out[3 * s + 1] = h_out[s].y;
+        out[3 * s + 2] = h_out[s].z;
+    }
+    cleanup();
+    return SA_OK;
+}
+
+uint64_t sa_cuda_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+}  // extern "C"

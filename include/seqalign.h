@@ -132,14 +132,16 @@ typedef struct sa_blob_header {
     uint32_t off_seqtab; /* sa_seq_desc[nseq]                                       */
     uint32_t off_items;  /* sa_item[nitems], grouped by rank, costliest first       */
     uint32_t off_seq2;   /* uint8 codes, each sequence 16-byte aligned, zero padded */
-    uint32_t max_rows_padded;
+    uint32_t max_rows_padded;  /* largest padded row count of any sequence          */
+    uint32_t max_window_bytes; /* largest Seq1 window any item stages (16-B multiple) */
     uint32_t chunk_bytes; /* fabric broadcast granularity */
     uint32_t nchunks;
+    uint32_t pad0;
     uint64_t total_cells;  /* sum over sequences of candidates                 */
     uint64_t padded_cells; /* cells the tiling actually evaluates              */
     uint32_t world;        /* number of GPUs the item list is partitioned for  */
     uint32_t rank_first_item[SA_MAX_WORLD + 1]; /* rank r owns items [r], [r+1]) */
-    uint32_t reserved[22];
+    uint32_t reserved[20];
 } sa_blob_header; /* 256 bytes */
 
 typedef struct sa_seq_desc {
@@ -188,14 +190,15 @@ int sa_cuda_scratch_init(void* d_scratch, size_t bytes, void* stream);
 
 /* Solve a packed blob that already sits in device memory.
  *   d_blob     device pointer to the blob (16-byte aligned)
+ *   header     HOST copy of the blob's first 256 bytes (sizes the launch; no D2H needed)
  *   d_out      device int32[4*nseq]: score, n, k, 0 per sequence
- *   d_scratch  device scratch of sa_cuda_scratch_bytes(nseq), zeroed once
- *   nseq/nitems as in the blob header (host copies; no D2H needed to launch)
+ *   d_scratch  device scratch of sa_cuda_scratch_bytes(nseq), zeroed once with
+ *              sa_cuda_scratch_init (the kernel leaves it zeroed again)
  *   stream     cudaStream_t (NULL = default stream)
- * One kernel launch, no allocation, no synchronisation.
+ * One kernel launch on the current device, no allocation, no synchronisation.
  * Replaces cudaFunctions.cu:178-242 (per-row malloc+launch+sync) and :63-176. */
-int sa_cuda_solve_blob(const void* d_blob, int32_t* d_out, void* d_scratch,
-                       uint32_t nseq, uint32_t nitems, void* stream);
+int sa_cuda_solve_blob(const void* d_blob, const sa_blob_header* header, int32_t* d_out,
+                       void* d_scratch, void* stream);
 
 /* Convenience: plan+pack `p`, upload, solve, download (allocates; synchronous).
  * out: int32[3*nseq]. */

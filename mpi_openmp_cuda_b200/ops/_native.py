@@ -24,10 +24,10 @@ class BlobHeader(C.Structure):
         ("len1", C.c_uint32), ("len1_padded", C.c_uint32), ("nseq", C.c_uint32), ("nitems", C.c_uint32),
         ("off_lut", C.c_uint32), ("off_seq1", C.c_uint32), ("off_seqtab", C.c_uint32),
         ("off_items", C.c_uint32), ("off_seq2", C.c_uint32),
-        ("max_rows_padded", C.c_uint32), ("chunk_bytes", C.c_uint32), ("nchunks", C.c_uint32),
+        ("max_rows_padded", C.c_uint32), ("max_window_bytes", C.c_uint32), ("chunk_bytes", C.c_uint32), ("nchunks", C.c_uint32), ("pad0", C.c_uint32),
         ("total_cells", C.c_uint64), ("padded_cells", C.c_uint64),
         ("world", C.c_uint32), ("rank_first_item", C.c_uint32 * (SA_MAX_WORLD + 1)),
-        ("reserved", C.c_uint32 * 22),
+        ("reserved", C.c_uint32 * 20),
     ]
 
 

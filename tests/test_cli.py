@@ -1,0 +1,50 @@
+"""`final` keeps the reference's stdin->stdout contract (main.c:46-244, makefile:11)."""
+import json
+import subprocess
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+@pytest.fixture(scope="module")
+def final_bin():
+    exe = ROOT / "final"
+    if not exe.exists():
+        subprocess.run(["make", "-C", str(ROOT), "core"], check=True, capture_output=True)
+        subprocess.run(["g++", "-O2", "-std=c++17", "-Iinclude", "-o", "final", "csrc/host/final_main.cpp",
+                        "-Lmpi_openmp_cuda_b200/_lib", "-lseqalign_core", "-ldl",
+                        "-Wl,-rpath,$ORIGIN/mpi_openmp_cuda_b200/_lib"], cwd=ROOT, check=True)
+    return exe
+
+
+@pytest.mark.parametrize("i", [1, 2, 3, 4, 5, 6])
+def test_cpu_oracle_mode_is_byte_identical(final_bin, shipped_inputs, i):
+    path, gold = shipped_inputs[i]
+    out = subprocess.run([str(final_bin), "--cpu-oracle"], stdin=open(path, "rb"), capture_output=True, check=True)
+    assert out.stdout == gold.read_bytes()
+    assert out.stderr == b""
+
+
+def test_timing_json_goes_to_side_file(final_bin, shipped_inputs, tmp_path):
+    path, gold = shipped_inputs[1]
+    tj = tmp_path / "t.json"
+    out = subprocess.run([str(final_bin), "--cpu-oracle", "--timing-json", str(tj)], stdin=open(path, "rb"),
+                         capture_output=True, check=True)
+    assert out.stdout == gold.read_bytes()  # stdout stays byte-identical
+    info = json.loads(tj.read_text())
+    assert info["nseq"] == 10 and info["candidates"] == 5006
+
+
+def test_parse_error_is_nonzero_exit(final_bin):
+    out = subprocess.run([str(final_bin), "--cpu-oracle"], input=b"1 2 3 4 ABC 3 AB", capture_output=True)
+    assert out.returncode != 0 and out.stdout == b"" and b"expected 3 sequences" in out.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("i", [1, 2, 3, 4, 5, 6])
+def test_gpu_mode_is_byte_identical(final_bin, shipped_inputs, i):
+    path, gold = shipped_inputs[i]
+    out = subprocess.run([str(final_bin)], stdin=open(path, "rb"), capture_output=True, check=True)
+    assert out.stdout == gold.read_bytes()

@@ -1,0 +1,108 @@
+"""sm_100a scoring kernel vs the CPU oracle (plain reference of the same op) and the goldens."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from mpi_openmp_cuda_b200 import Problem, format_results, solve_text
+from mpi_openmp_cuda_b200.models.synthetic import random_problem
+from mpi_openmp_cuda_b200.ops import plan
+from mpi_openmp_cuda_b200.ops.oracle import solve_cpu
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def solver():
+    from mpi_openmp_cuda_b200.models.alignment import AlignmentSolver
+
+    return AlignmentSolver("cuda:0")
+
+
+def test_cuda_library_is_loaded_not_a_fallback():
+    from mpi_openmp_cuda_b200.ops import _native
+
+    lib = _native.cuda()
+    assert "libseqalign_cuda.so" in lib._name
+
+
+@pytest.mark.parametrize("i", [1, 2, 3, 4, 5, 6])
+def test_golden_outputs(solver, shipped_inputs, i):
+    path, gold = shipped_inputs[i]
+    assert format_results(solver.solve(Problem.from_file(path))) == gold.read_bytes()
+
+
+def test_solve_text_contract(shipped_inputs):
+    path, gold = shipped_inputs[6]
+    assert solve_text(path.read_bytes(), device="cuda:0") == gold.read_bytes()
+
+
+def test_repeated_launches_reuse_self_cleaning_scratch(solver, shipped_inputs):
+    from mpi_openmp_cuda_b200.ops.score import launch_count
+
+    p3, p4 = Problem.from_file(shipped_inputs[3][0]), Problem.from_file(shipped_inputs[4][0])
+    r3, r4 = solve_cpu(p3), solve_cpu(p4)
+    before = launch_count()
+    for _ in range(5):
+        assert np.array_equal(solver.solve(p3), r3)
+        assert np.array_equal(solver.solve(p4), r4)
+    assert launch_count() - before == 10  # one kernel per solve
+
+
+EDGE = [
+    ("ABCDEFGH", ["A"]),
+    ("ABCDEFGH", ["AB", "ABC"]),
+    ("ABCDEFGH", ["ABCDEFGH"]),
+    ("ABCDEFGH", ["ABCDEFG"]),
+    ("ABC", ["ABCD", "AB"]),
+    ("AB-CD*EF", ["-CD", "B-C*"]),
+    ("A" * 700, ["A" * 5, "A" * 300, "B" * 40]),
+]
+
+
+@pytest.mark.parametrize("seq1,seqs", EDGE)
+def test_edge_shapes(solver, seq1, seqs):
+    p = Problem.from_parts((5, 1, 2, 3), seq1, seqs)
+    assert np.array_equal(solver.solve(p), solve_cpu(p, "fast"))
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_random_vs_oracle(solver, seed):
+    rng = np.random.default_rng(200 + seed)
+    w = tuple(int(x) for x in rng.integers(0, 40, size=4))
+    len1 = int(rng.integers(30, 3000))
+    p = random_problem(48, len1=len1, len2_range=(1, min(len1 + 3, 2000)), weights=w, seed=seed)
+    assert np.array_equal(solver.solve(p), solve_cpu(p, "fast"))
+
+
+def test_len2_above_1024_is_deterministic(solver):
+    # the reference races across two blocks for len2 > 1024 (cudaFunctions.cu:116-168)
+    p = random_problem(8, len1=2900, len2_range=(1025, 1999), seed=5)
+    ref = solve_cpu(p, "fast")
+    for _ in range(3):
+        assert np.array_equal(solver.solve(p), ref)
+
+
+def test_many_sequences(solver):
+    p = random_problem(3000, len1=800, len2_range=(20, 500), seed=11)
+    assert np.array_equal(solver.solve(p), solve_cpu(p, "fast"))
+
+
+def test_beyond_reference_caps(solver):
+    p = random_problem(3, len1=9000, len2_range=(3000, 6000), seed=2)
+    assert np.array_equal(solver.solve(p), solve_cpu(p, "fast"))
+
+
+def test_c_abi_convenience_entry(shipped_inputs):
+    from mpi_openmp_cuda_b200.ops import _native as N
+
+    p = Problem.from_file(shipped_inputs[1][0])
+    out = np.zeros((p.nseq, 3), dtype=np.int32)
+    N.check(N.cuda().sa_cuda_solve_problem(p.handle, out.ctypes.data_as(C.POINTER(C.c_int32)), 0))
+    assert np.array_equal(out, solve_cpu(p, "fast"))
+
+
+def test_cpu_walk_and_gpu_agree_on_blob(solver, shipped_inputs):
+    p = Problem.from_file(shipped_inputs[3][0])
+    blob = solver.pack(p)
+    assert np.array_equal(solver.solve_packed(blob), plan.execute_blob_cpu(blob))

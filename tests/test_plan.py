@@ -1,0 +1,114 @@
+"""Planner/packer + CPU walk of the packed blob (the GPU kernel's tile logic on the host)."""
+import numpy as np
+import pytest
+
+from mpi_openmp_cuda_b200 import Problem, format_results
+from mpi_openmp_cuda_b200.models.synthetic import random_problem
+from mpi_openmp_cuda_b200.ops import plan
+from mpi_openmp_cuda_b200.ops._native import NativeError, SA_ERR_UNSUPPORTED
+from mpi_openmp_cuda_b200.ops.oracle import solve_cpu
+
+
+@pytest.mark.parametrize("i", [1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("world", [1, 2, 8])
+def test_blob_walk_matches_golden(shipped_inputs, i, world):
+    path, gold = shipped_inputs[i]
+    blob = plan.plan_pack(Problem.from_file(path), world)
+    assert format_results(plan.execute_blob_cpu(blob)) == gold.read_bytes()
+
+
+def test_header_and_alignment(shipped_inputs):
+    blob = plan.plan_pack(Problem.from_file(shipped_inputs[3][0]), 4)
+    h = blob.header
+    assert h.total_bytes == blob.nbytes and h.nseq == 32 and h.world == 4
+    assert h.off_lut % 16 == 0 and h.off_seq1 % 16 == 0 and h.off_seq2 % 16 == 0
+    tab = blob.seq_table()
+    assert all(int(o) % 16 == 0 for o in tab["off"])
+    assert int(tab["ntiles"].sum()) == h.nitems
+    first = list(h.rank_first_item)[:5]
+    assert first[0] == 0 and first[4] == h.nitems and first == sorted(first)
+
+
+def test_every_item_appears_once(shipped_inputs):
+    blob = plan.plan_pack(Problem.from_file(shipped_inputs[4][0]), 8)
+    items = blob.items()
+    seen = set((int(s), int(t)) for s, t in zip(items["seq"], items["tile"]))
+    assert len(seen) == blob.nitems
+    tab = blob.seq_table()
+    for s in range(blob.nseq):
+        for t in range(int(tab["ntiles"][s])):
+            assert (s, t) in seen
+
+
+def test_partition_balance_large():
+    p = random_problem(512, len1=900, len2_range=(50, 700), seed=3)
+    blob = plan.plan_pack(p, 8)
+    h, tab, items = blob.header, blob.seq_table(), blob.items()
+    cost = (256 << tab["wd_log2"].astype(np.int64)) * (16 >> tab["wd_log2"].astype(np.int64)) * tab["crow"].astype(np.int64)
+    loads = []
+    for r in range(8):
+        sl = items[h.rank_first_item[r] : h.rank_first_item[r + 1]]
+        loads.append(int(cost[sl["seq"]].sum()))
+        # whole sequences stay on one rank when sequences are plentiful
+        assert all(int(tab["home"][s]) == r for s in sl["seq"])
+    assert max(loads) <= 1.1 * (sum(loads) / 8)
+
+
+def test_scarce_sequences_are_split_by_tile(shipped_inputs):
+    blob = plan.plan_pack(Problem.from_file(shipped_inputs[2][0]), 8)  # one sequence
+    assert blob.nitems >= 1
+    p = Problem.from_parts((1, 1, 1, 1), "A" * 2900, ["C" * 100])
+    blob = plan.plan_pack(p, 4)
+    h = blob.header
+    counts = [h.rank_first_item[r + 1] - h.rank_first_item[r] for r in range(4)]
+    assert sum(counts) == blob.nitems and max(counts) - min(counts) <= 1
+
+
+EDGE = [
+    ("ABCDEFGH", ["A"]),             # len2 = 1: only k = 0 exists
+    ("ABCDEFGH", ["AB", "ABC"]),     # len2 in {2,3}: the reference drops classes here (Q8)
+    ("ABCDEFGH", ["ABCDEFGH"]),      # equal length
+    ("ABCDEFGH", ["ABCDEFG"]),       # len1 - 1: a single offset
+    ("ABC", ["ABCD", "AB"]),         # longer than Seq1 -> INT_MIN row, plus a normal row
+    ("AB-CD*EF", ["-CD", "B-C*"]),   # non-letter bytes
+]
+
+
+@pytest.mark.parametrize("seq1,seqs", EDGE)
+def test_edge_shapes(seq1, seqs):
+    p = Problem.from_parts((5, 1, 2, 3), seq1, seqs)
+    ref = solve_cpu(p, "naive")
+    for world in (1, 2):
+        assert np.array_equal(plan.execute_blob_cpu(plan.plan_pack(p, world)), ref)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_random_vs_oracle(seed):
+    rng = np.random.default_rng(100 + seed)
+    w = tuple(int(x) for x in rng.integers(0, 30, size=4))
+    len1 = int(rng.integers(30, 1400))
+    p = random_problem(10, len1=len1, len2_range=(1, min(len1 + 3, 1300)), weights=w, seed=seed)
+    assert np.array_equal(plan.execute_blob_cpu(plan.plan_pack(p, 1 + seed % 3)), solve_cpu(p, "fast"))
+
+
+def test_ties_heavy():
+    # constant sequences: every candidate ties; first (n=0,k=0) must win
+    p = Problem.from_parts((3, 1, 1, 1), "A" * 700, ["A" * 5, "A" * 300, "B" * 40])
+    assert np.array_equal(plan.execute_blob_cpu(plan.plan_pack(p)), solve_cpu(p, "fast"))
+
+
+def test_long_sequences_beyond_reference_caps():
+    p = random_problem(2, len1=5000, len2_range=(2500, 3000), seed=9)
+    assert np.array_equal(plan.execute_blob_cpu(plan.plan_pack(p)), solve_cpu(p, "fast"))
+
+
+def test_unsupported_inputs_are_reported():
+    with pytest.raises(NativeError) as e:
+        plan.plan_pack(Problem.from_parts((1, 1, 1, 1), "A" * 10000, ["B" * 9000]))
+    assert e.value.code == SA_ERR_UNSUPPORTED
+    with pytest.raises(NativeError) as e:
+        plan.plan_pack(Problem.from_parts((1 << 28, 1, 1, 1), "A" * 100, ["B" * 50]))
+    assert e.value.code == SA_ERR_UNSUPPORTED
+    with pytest.raises(NativeError) as e:
+        plan.plan_pack(Problem.from_parts((1, 1, 1, 1), "A-*+/=", ["B!?"]))  # > 5 distinct non-letters
+    assert e.value.code == SA_ERR_UNSUPPORTED
