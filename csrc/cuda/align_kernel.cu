@@ -489,4 +489,68 @@ int sa_cuda_solve_problem(const sa_problem* prob, int32_t* out, int device) {
 
 uint64_t sa_cuda_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
+// ---------------------------------------------------------------------------------------
+// Fixed-capacity variant for callers that must not allocate device memory.
+//
+// Who that is: code that runs after the host application has handed every byte of HBM to
+// its own pool (an inference server's plug-in hook, a framework custom op executing under a
+// caching allocator it must not bypass) and code on a latency-critical path where the
+// device-wide synchronisation hidden inside cudaMalloc/cudaFree is not acceptable. Such a
+// caller can still provide the problem blob and the result table (they are its inputs and
+// outputs), but it has nowhere to get the solver's private scratch from.
+//
+// So the scratch (argmax keys, arrival counters, work-queue words) lives in the library
+// image itself: a file-scope device array, one copy per GPU that loads this library, held
+// until the process exits. It is sized for SA_NOALLOC_MAX_SEQ sequences — 49,408 bytes.
+//
+// The array's name below is only a host-side handle. Its device address is looked up once
+// per device with cudaGetSymbolAddress while that device is current, and that address is what
+// the kernel receives.
+constexpr size_t kStaticScratchBytes =
+    ((size_t)SA_NOALLOC_MAX_SEQ * 8 + 255) / 256 * 256 + ((size_t)SA_NOALLOC_MAX_SEQ * 4 + 255) / 256 * 256 + 256;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+namespace {
+std::mutex g_static_mu;
+void* g_static_scratch_addr[64] = {nullptr};
+}  // namespace
+
+int sa_cuda_solve_blob_noalloc(const void* d_blob, const sa_blob_header* header, int32_t* d_out, void* stream) {
+    if (!d_blob || !header || !d_out) {
+        sa_set_last_error("sa_cuda_solve_blob_noalloc: null argument");
+        return SA_ERR_ARG;
+    }
+    if (header->nseq > SA_NOALLOC_MAX_SEQ) {
+        char msg[160];
+        std::snprintf(msg, sizeof(msg),
+                      "sa_cuda_solve_blob_noalloc: %u sequences exceed the built-in scratch capacity of %u; "
+                      "use sa_cuda_solve_blob with caller-provided scratch",
+                      header->nseq, (unsigned)SA_NOALLOC_MAX_SEQ);
+        sa_set_last_error(msg);
+        return SA_ERR_TOO_LARGE;
+    }
+    int dev = 0;
+    SA_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) {
+        sa_set_last_error("sa_cuda_solve_blob_noalloc: device index out of range");
+        return SA_ERR_ARG;
+    }
+    void* scratch = nullptr;
+    {
+        // First call on this device: resolve the array's device address (`dev` is current).
+        std::lock_guard<std::mutex> lock(g_static_mu);
+        if (!g_static_scratch_addr[dev]) {
+            void* ptr = nullptr;
+            SA_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_static_scratch));
+            g_static_scratch_addr[dev] = ptr;
+        }
+        scratch = g_static_scratch_addr[dev];
+    }
+    // The array keeps whatever the previous call left. A call that ran to completion leaves
+    // zeros, one that was torn down half-way does not, so clear the part this launch reads.
+    const size_t used = sa_cuda_scratch_bytes(header->nseq);
+    SA_CUDA_TRY(cudaMemsetAsync(scratch, 0, used, static_cast<cudaStream_t>(stream)));
+    return sa_cuda_solve_blob(d_blob, header, d_out, scratch, stream);
+}
+
 }  // extern "C"

@@ -204,6 +204,31 @@ int sa_cuda_solve_blob(const void* d_blob, const sa_blob_header* header, int32_t
  * out: int32[3*nseq]. */
 int sa_cuda_solve_problem(const sa_problem* p, int32_t* out, int device);
 
+/* Largest problem (in sequences) the allocation-free entry point below accepts. */
+#define SA_NOALLOC_MAX_SEQ 4096u
+
+/* Same solve as sa_cuda_solve_blob, for callers that cannot allocate device memory.
+ * (No counterpart in the reference: it cudaMallocs per row, cudaFunctions.cu:189-206.)
+ *
+ * Meant for code that runs where HBM already belongs to someone else's pool — a plug-in or
+ * custom op executing inside a server or framework that owns the allocator — or where the
+ * device-wide stall of cudaMalloc/cudaFree cannot be afforded. You pass the blob and the
+ * result table as usual; the solver's scratch is a 49,408-byte array compiled into
+ * libseqalign_cuda.so (each GPU that loads the library carries one copy until exit).
+ *
+ *  - header->nseq must be <= SA_NOALLOC_MAX_SEQ, otherwise SA_ERR_TOO_LARGE is returned and
+ *    nothing is launched.
+ *  - Makes no cudaMalloc / cudaFree / allocating library call. It enqueues one small memset
+ *    and one kernel on `stream`, on the current device.
+ *  - The first call on each device looks up the array's device address
+ *    (cudaGetSymbolAddress); make that first call outside any stream capture.
+ *  - All calls on a device share the one array, and it keeps the previous call's contents;
+ *    every call therefore clears the part it uses first. Two calls whose GPU work overlaps
+ *    (different streams, no dependency) race on it — serialise them, or give the second one
+ *    its own scratch through sa_cuda_solve_blob. */
+int sa_cuda_solve_blob_noalloc(const void* d_blob, const sa_blob_header* header, int32_t* d_out,
+                               void* stream);
+
 /* Number of kernel launches issued by this library in this process. */
 uint64_t sa_cuda_launch_count(void);
 

@@ -15,6 +15,7 @@ SA_OK = 0
 SA_ERR_UNSUPPORTED = 3
 SA_ERR_TOO_LARGE = 6
 SA_MAX_WORLD = 16
+SA_NOALLOC_MAX_SEQ = 4096
 
 
 class BlobHeader(C.Structure):
@@ -103,6 +104,7 @@ def cuda() -> C.CDLL:
     lib.sa_cuda_scratch_init.argtypes = [vp, sz, vp]
     lib.sa_cuda_solve_blob.argtypes = [vp, C.POINTER(BlobHeader), vp, vp, vp]
     lib.sa_cuda_solve_problem.argtypes = [vp, C.POINTER(C.c_int32), C.c_int]
+    lib.sa_cuda_solve_blob_noalloc.argtypes = [vp, C.POINTER(BlobHeader), vp, vp]
     lib.sa_cuda_launch_count.restype = C.c_uint64
     return lib
 
