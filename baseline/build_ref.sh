@@ -1,0 +1,59 @@
+#!/bin/bash
+# Build the UNMODIFIED reference (nmiz1987/MPI-OPENMP-CUDA) into baseline/_ref (git-ignored).
+#
+#   1. try the prescribed `pip install ... --target baseline/_ref /root/reference` and log the outcome
+#      (it cannot succeed: the reference is a makefile project, not a Python distribution);
+#   2. build the MPI stand-in (baseline/mpi_shim) — the image has no MPI;
+#   3. copy the reference's own sources verbatim into baseline/_ref/src;
+#   4. compile them with the reference makefile's exact commands and flags (makefile:2-4), only the
+#      hard-coded /usr/local/cuda-11.0 path replaced by this image's CUDA_HOME:
+#        bin/final        — as shipped: no -arch  => sm_52 SASS + compute_52 PTX (PTX-JIT on B200)
+#        bin/final_sm100  — same sources, nvcc -arch=sm_100 (the "best case" for the reference)
+set -u
+HERE="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
+REF_SRC="${REF_SRC:-/root/reference}"
+OUT="$HERE/_ref"
+CUDA_HOME="${CUDA_HOME:-/usr/local/cuda}"
+export PATH="$CUDA_HOME/bin:$PATH"
+mkdir -p "$OUT/src" "$OUT/bin" "$OUT/shim" "$OUT/log"
+
+echo "== step 1: pip install (expected to fail)" | tee "$OUT/log/pip_install.log"
+( python -m pip install --no-index --no-build-isolation --find-links /opt/wheelhouse \
+    --target "$OUT/pip_target" "$REF_SRC" 2>&1 | tail -5 ) >> "$OUT/log/pip_install.log"
+echo "pip exit: ${PIPESTATUS[0]}" >> "$OUT/log/pip_install.log"
+
+echo "== step 2: MPI stand-in"
+cp "$HERE/mpi_shim/mpi.h" "$HERE/mpi_shim/shim_common.h" "$HERE/mpi_shim/mpicxx" "$OUT/shim/"
+g++ -O2 -fPIC -shared -o "$OUT/shim/libmpishim.so" "$HERE/mpi_shim/mpi_shim.cpp" -I"$HERE/mpi_shim" -lpthread || exit 1
+g++ -O2 -o "$OUT/bin/mpiexec" "$HERE/mpi_shim/mpiexec.cpp" -I"$HERE/mpi_shim" -lpthread || exit 1
+
+echo "== step 3: reference sources (verbatim)"
+if [ -d "$REF_SRC" ]; then
+    cp "$REF_SRC/main.c" "$REF_SRC/cudaFunctions.cu" "$REF_SRC/myProto.h" "$REF_SRC/makefile" "$OUT/src/"
+    mkdir -p "$OUT/src/inc"
+    cp "$REF_SRC/inc/helper_cuda.h" "$REF_SRC/inc/helper_string.h" "$OUT/src/inc/"
+    ( cd "$REF_SRC" && sha256sum main.c cudaFunctions.cu myProto.h makefile ) > "$OUT/log/source_sha256.txt"
+elif [ ! -f "$OUT/src/main.c" ]; then
+    echo "no reference sources at $REF_SRC and none cached in $OUT/src" >&2
+    exit 1
+fi
+
+echo "== step 4: compile with the makefile's commands"
+cd "$OUT/src" || exit 1
+MPICXX="$OUT/shim/mpicxx"
+build_variant() {   # $1 = output name, $2.. = extra nvcc flags
+    local out="$1"; shift
+    "$MPICXX" -fopenmp -c main.c 2> "$OUT/log/main_c.warnings" || return 1                  # makefile:2
+    nvcc "$@" -I./inc -c cudaFunctions.cu 2> "$OUT/log/nvcc_$out.warnings" || return 1      # makefile:3
+    "$MPICXX" -fopenmp -o "$OUT/bin/$out" main.o cudaFunctions.o \
+        "$CUDA_HOME/lib64/libcudart_static.a" -ldl -lrt -Wl,-rpath,'$ORIGIN/../shim' || return 1   # makefile:4
+}
+build_variant final || exit 1
+build_variant final_sm100 -arch=sm_100 || exit 1
+rm -f main.o cudaFunctions.o
+cuobjdump -lelf "$OUT/bin/final" > "$OUT/log/final_archs.txt" 2>&1
+cuobjdump -lptx "$OUT/bin/final" >> "$OUT/log/final_archs.txt" 2>&1
+cuobjdump -lelf "$OUT/bin/final_sm100" > "$OUT/log/final_sm100_archs.txt" 2>&1
+ls -la "$OUT/bin"
+cat "$OUT/log/final_archs.txt" "$OUT/log/final_sm100_archs.txt"
+echo "reference build ok"
