@@ -216,4 +216,11 @@ def run_reference(args):
 
 if __name__ == "__main__":
     a = parse_args()
-    sys.exit(run_reference(a) if a.impl == "reference" else run_ours(a))
+    # exactly ONE line on stdout: keep library banners (e.g. "NCCL version ...") off fd 1
+    sys.stdout.flush()
+    _real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(_real, "w")
+    rc = run_reference(a) if a.impl == "reference" else run_ours(a)
+    sys.stdout.flush()
+    sys.exit(rc)

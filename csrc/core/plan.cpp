@@ -213,7 +213,9 @@ int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, siz
     h->off_seq2 = off_seq2;
     h->max_rows_padded = max_rows;
     h->max_window_bytes = max_window;
-    h->chunk_bytes = 1u << 16;
+    // fabric broadcast granularity: 8 KiB (so that even a 30 KB blob is pushed by several CTAs
+    // at once), grown so that a blob never needs more flags than exist
+    h->chunk_bytes = std::max<uint32_t>(1u << 13, round_up((uint32_t)((total + SA_FABRIC_MAX_CHUNKS - 1) / SA_FABRIC_MAX_CHUNKS), 1u << 13));
     h->nchunks = (uint32_t)((total + h->chunk_bytes - 1) / h->chunk_bytes);
     h->total_cells = total_cells;
     h->padded_cells = padded_cells;
@@ -267,43 +269,60 @@ void sa_blob_free(void* blob) { std::free(blob); }
 // CPU walk of the blob with the kernel's exact decomposition (see align_kernel.cu):
 // per item, 16 "warps" = wd offset groups x wr row chunks; per lane R+1 running prefixes and R
 // running maxima; per-chunk results combined in row order; best (score, smallest n) folded
-// into a packed 64-bit key; when the last tile of a sequence lands, the winning diagonal is
-// rescanned for the first k.
-int sa_blob_execute_cpu(const void* blob, size_t blob_bytes, int32_t* out4) {
+// into a packed 64-bit key. `sa_blob_score_items_cpu` does that for a range of items (one rank's
+// share) and max-merges into keys[nseq]; `sa_blob_finalize_cpu` turns complete keys into
+// (score, n, k) by rescanning each winning diagonal for the first k.
+namespace {
+
+struct BlobView {
+    const unsigned char* base;
+    const sa_blob_header* h;
+    const int32_t* lut;
+    const unsigned char* seq1;
+    const sa_seq_desc* tab;
+    const sa_item* items;
+    int32_t value(unsigned code2, unsigned c4) const { return lut[code2 * SA_ALPHABET + (c4 >> 2)]; }
+};
+
+int open_blob(const void* blob, size_t blob_bytes, BlobView* v) {
+    if (!blob || blob_bytes < sizeof(sa_blob_header)) {
+        sa::set_error("blob: bad argument");
+        return SA_ERR_ARG;
+    }
+    v->base = static_cast<const unsigned char*>(blob);
+    v->h = reinterpret_cast<const sa_blob_header*>(v->base);
+    if (v->h->magic != SA_BLOB_MAGIC || v->h->version != SA_BLOB_VERSION || v->h->total_bytes > blob_bytes) {
+        sa::set_error("blob: not a blob of this version");
+        return SA_ERR_ARG;
+    }
+    v->lut = reinterpret_cast<const int32_t*>(v->base + v->h->off_lut);
+    v->seq1 = v->base + v->h->off_seq1;
+    v->tab = reinterpret_cast<const sa_seq_desc*>(v->base + v->h->off_seqtab);
+    v->items = reinterpret_cast<const sa_item*>(v->base + v->h->off_items);
+    return SA_OK;
+}
+
+}  // namespace
+
+int sa_blob_score_items_cpu(const void* blob, size_t blob_bytes, uint32_t first_item, uint32_t last_item,
+                            uint64_t* keys) {
     using namespace sa;
-    if (!blob || !out4 || blob_bytes < sizeof(sa_blob_header)) {
-        set_error("sa_blob_execute_cpu: bad argument");
+    BlobView b;
+    int rc = open_blob(blob, blob_bytes, &b);
+    if (rc != SA_OK) return rc;
+    if (!keys || first_item > last_item || last_item > b.h->nitems) {
+        set_error("sa_blob_score_items_cpu: bad item range");
         return SA_ERR_ARG;
     }
-    const unsigned char* base = static_cast<const unsigned char*>(blob);
-    const sa_blob_header* h = reinterpret_cast<const sa_blob_header*>(base);
-    if (h->magic != SA_BLOB_MAGIC || h->version != SA_BLOB_VERSION || h->total_bytes > blob_bytes) {
-        set_error("sa_blob_execute_cpu: not a blob of this version");
-        return SA_ERR_ARG;
-    }
-    const int32_t* lut = reinterpret_cast<const int32_t*>(base + h->off_lut);
-    const unsigned char* seq1 = base + h->off_seq1;
-    const sa_seq_desc* tab = reinterpret_cast<const sa_seq_desc*>(base + h->off_seqtab);
-    const sa_item* items = reinterpret_cast<const sa_item*>(base + h->off_items);
-    std::vector<uint64_t> key(h->nseq, 0);
-    std::vector<uint32_t> cnt(h->nseq, 0);
-    auto value = [&](unsigned code2, unsigned c4) { return lut[code2 * SA_ALPHABET + (c4 >> 2)]; };
-
-    for (uint32_t s = 0; s < h->nseq; ++s)
-        if (tab[s].ntiles == 0) {
-            out4[4 * s] = INT_MIN;
-            out4[4 * s + 1] = out4[4 * s + 2] = out4[4 * s + 3] = 0;
-        }
-
     std::vector<int32_t> csum((size_t)kWarps * (kR + 1) * 32), cmax((size_t)kWarps * kR * 32);
-    for (uint32_t it = 0; it < h->nitems; ++it) {
-        const uint32_t s = items[it].seq, tile = items[it].tile;
-        const sa_seq_desc& sd = tab[s];
-        const unsigned char* s2 = base + sd.off;
+    for (uint32_t it = first_item; it < last_item; ++it) {
+        const uint32_t s = b.items[it].seq, tile = b.items[it].tile;
+        const sa_seq_desc& sd = b.tab[s];
+        const unsigned char* s2 = b.base + sd.off;
         const uint32_t wd = 1u << sd.wd_log2, wr = kWarps / wd, crow = sd.crow;
         const uint32_t tn = kWarpDiag * wd, n0 = tile * tn;
-        if ((uint64_t)n0 + wr * crow + tn > h->len1_padded) {
-            set_error("sa_blob_execute_cpu: window outside padded Seq1");
+        if ((uint64_t)n0 + wr * crow + tn > b.h->len1_padded) {
+            set_error("sa_blob_score_items_cpu: window outside padded Seq1");
             return SA_ERR_ARG;
         }
         for (uint32_t w = 0; w < kWarps; ++w) {
@@ -315,7 +334,7 @@ int sa_blob_execute_cpu(const void* blob, size_t blob_bytes, int32_t* out4) {
                 for (uint32_t r = 0; r < kR; ++r) best[r] = kNeg;
                 for (uint32_t i = q * crow; i < (q + 1) * crow; ++i) {
                     const unsigned code2 = s2[i];
-                    for (uint32_t r = 0; r <= kR; ++r) P[r] += value(code2, seq1[n0 + i + d0 + r]);
+                    for (uint32_t r = 0; r <= kR; ++r) P[r] += b.value(code2, b.seq1[n0 + i + d0 + r]);
                     for (uint32_t r = 0; r < kR; ++r) best[r] = std::max(best[r], P[r] - P[r + 1]);
                 }
                 for (uint32_t r = 0; r <= kR; ++r) csum[((size_t)w * (kR + 1) + r) * 32 + lane] = P[r];
@@ -343,40 +362,75 @@ int sa_blob_execute_cpu(const void* blob, size_t blob_bytes, int32_t* out4) {
                 tile_key = std::max(tile_key, pack_key(T1 + M, n));
             }
         }
-        key[s] = std::max(key[s], tile_key);
-        if (++cnt[s] == sd.ntiles) {
-            const int32_t best = (int32_t)((uint32_t)(key[s] >> 32) ^ 0x80000000u);
-            const uint32_t n = 0xFFFFFFFFu - (uint32_t)(key[s] & 0xFFFFFFFFu);
-            int32_t k = 0;
-            if (sd.ndiag != 0) {
-                int32_t T0 = 0, T1 = 0;
-                for (uint32_t i = 0; i < sd.len; ++i) {
-                    T0 += value(s2[i], seq1[n + i]);
-                    T1 += value(s2[i], seq1[n + i + 1]);
-                }
-                if (T0 != best) {
-                    int32_t S = 0;
-                    k = -1;
-                    for (uint32_t i = 0; i + 1 < sd.len; ++i) {
-                        S += value(s2[i], seq1[n + i]) - value(s2[i], seq1[n + i + 1]);
-                        if (T1 + S == best) {
-                            k = (int32_t)(i + 1);
-                            break;
-                        }
-                    }
-                    if (k < 0) {
-                        set_error("sa_blob_execute_cpu: winning diagonal does not reproduce the best score");
-                        return SA_ERR_ARG;
-                    }
-                }
-            }
-            out4[4 * s] = best;
-            out4[4 * s + 1] = (int32_t)n;
-            out4[4 * s + 2] = k;
-            out4[4 * s + 3] = 0;
-        }
+        keys[s] = std::max(keys[s], tile_key);
     }
     return SA_OK;
+}
+
+int sa_blob_finalize_cpu(const void* blob, size_t blob_bytes, const uint64_t* keys, int32_t* out4) {
+    using namespace sa;
+    BlobView b;
+    int rc = open_blob(blob, blob_bytes, &b);
+    if (rc != SA_OK) return rc;
+    if (!keys || !out4) {
+        set_error("sa_blob_finalize_cpu: null argument");
+        return SA_ERR_ARG;
+    }
+    for (uint32_t s = 0; s < b.h->nseq; ++s) {
+        const sa_seq_desc& sd = b.tab[s];
+        if (sd.ntiles == 0) {
+            out4[4 * s] = INT_MIN;
+            out4[4 * s + 1] = out4[4 * s + 2] = out4[4 * s + 3] = 0;
+            continue;
+        }
+        const unsigned char* s2 = b.base + sd.off;
+        const int32_t best = (int32_t)((uint32_t)(keys[s] >> 32) ^ 0x80000000u);
+        const uint32_t n = 0xFFFFFFFFu - (uint32_t)(keys[s] & 0xFFFFFFFFu);
+        int32_t k = 0;
+        if (sd.ndiag != 0) {
+            if (n >= (uint32_t)sd.ndiag) {
+                set_error("sa_blob_finalize_cpu: key holds no valid offset (were all items scored?)");
+                return SA_ERR_ARG;
+            }
+            int32_t T0 = 0, T1 = 0;
+            for (uint32_t i = 0; i < sd.len; ++i) {
+                T0 += b.value(s2[i], b.seq1[n + i]);
+                T1 += b.value(s2[i], b.seq1[n + i + 1]);
+            }
+            if (T0 != best) {
+                int32_t S = 0;
+                k = -1;
+                for (uint32_t i = 0; i + 1 < sd.len; ++i) {
+                    S += b.value(s2[i], b.seq1[n + i]) - b.value(s2[i], b.seq1[n + i + 1]);
+                    if (T1 + S == best) {
+                        k = (int32_t)(i + 1);
+                        break;
+                    }
+                }
+                if (k < 0) {
+                    set_error("sa_blob_finalize_cpu: winning diagonal does not reproduce the best score");
+                    return SA_ERR_ARG;
+                }
+            }
+        }
+        out4[4 * s] = best;
+        out4[4 * s + 1] = (int32_t)n;
+        out4[4 * s + 2] = k;
+        out4[4 * s + 3] = 0;
+    }
+    return SA_OK;
+}
+
+int sa_blob_execute_cpu(const void* blob, size_t blob_bytes, int32_t* out4) {
+    if (!blob || !out4 || blob_bytes < sizeof(sa_blob_header)) {
+        sa::set_error("sa_blob_execute_cpu: bad argument");
+        return SA_ERR_ARG;
+    }
+    const sa_blob_header* h = static_cast<const sa_blob_header*>(blob);
+    std::vector<uint64_t> keys(h->nseq ? h->nseq : 1, 0);
+    int rc = sa_blob_score_items_cpu(blob, blob_bytes, 0, h->nitems, keys.data());
+    if (rc != SA_OK) return rc;
+    return sa_blob_finalize_cpu(blob, blob_bytes, keys.data(), out4);
 }
 
 }  // extern "C"

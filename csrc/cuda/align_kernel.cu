@@ -49,7 +49,17 @@ struct KParams {
     uint32_t item_begin, item_end;
     uint32_t s2_cap, win_cap;   // shared-memory capacities (bytes, multiples of 16)
     uint32_t write_empty;       // 1: this launch writes the rows of candidate-free sequences
+    // ---- fabric (multi-GPU) launches only; see sa_cuda_fabric_solve
+    uint32_t rank, world, epoch, use_mc;
+    unsigned char* peer[SA_MAX_WORLD];  // every rank's symmetric buffer as mapped into this process
+    unsigned char* mc;                  // NVLS multicast alias of the same buffer, or null
+    uint32_t off_ctrl, off_key, off_cnt, off_out, off_blob;
+    unsigned long long timeout_ns;
 };
+
+// Words of the control block at the start of every rank's symmetric buffer.
+constexpr uint32_t kCtlNext = 0, kCtlCtasDone = 1, kCtlRanksDone = 2, kCtlError = 3, kCtlFlags = 64;
+constexpr uint32_t kMaxChunks = SA_FABRIC_MAX_CHUNKS;
 
 // ------------------------------------------------------------------ PTX helpers
 
@@ -84,6 +94,38 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
                  : "memory");
 }
 
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+// One store that the NVSwitch replicates into every GPU bound to the multicast object.
+__device__ __forceinline__ void multimem_st_v4(void* mc_addr, int4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "r"(v.x), "r"(v.y),
+                 "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// Bounded wait for a flag written by a peer GPU (never an unbounded spin: a dead peer must not
+// hang this GPU). Returns false on timeout.
+__device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t epoch, unsigned long long timeout_ns) {
+    if ((int)(ld_acquire_sys(flag) - epoch) >= 0) return true;
+    const unsigned long long t0 = global_ns();
+    for (;;) {
+        if ((int)(ld_acquire_sys(flag) - epoch) >= 0) return true;
+        __nanosleep(64);
+        if (global_ns() - t0 > timeout_ns) return false;
+    }
+}
+
 __device__ __forceinline__ unsigned long long pack_key(int score, uint32_t n) {
     return ((unsigned long long)((uint32_t)score ^ 0x80000000u) << 32) | (unsigned long long)(0xFFFFFFFFu - n);
 }
@@ -96,7 +138,16 @@ __device__ __forceinline__ uint32_t byte_of(uint32_t lo, uint32_t hi, int k) {  
 
 // ------------------------------------------------------------------ the kernel
 
-__global__ void __launch_bounds__(kThreads, 2) sa_score_kernel(const KParams p) {
+// kFabric = false: one GPU owns everything (p.key/p.cnt/p.out/p.ctrl are local).
+// kFabric = true : one of `world` cooperating launches, one per GPU (see sa_cuda_fabric_solve):
+//   rank 0 broadcasts the blob from inside the kernel (NVLS multicast store or per-peer P2P stores,
+//   chunk by chunk, each chunk followed by a release flag), the other ranks start scoring as soon
+//   as the chunks they need have landed; per-sequence keys/counters live on the sequence's home
+//   rank and are updated with system-scope atomics over NVLink; results go straight into rank 0's
+//   table; the last CTA of every rank bumps rank 0's arrival counter and rank 0's last CTA waits
+//   for all of them. No MPI/NCCL call on either path (replaces main.c:149-152,174,195-197).
+template <bool kFabric>
+__device__ __forceinline__ void score_body(const KParams& p) {
     extern __shared__ __align__(16) unsigned char smem[];
     unsigned char* const lut_b = smem;
     unsigned char* const s2 = lut_b + kLutBytes;
@@ -110,43 +161,114 @@ __global__ void __launch_bounds__(kThreads, 2) sa_score_kernel(const KParams p) 
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
-    const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + hdr->off_seqtab);
-    const sa_item* const items = reinterpret_cast<const sa_item*>(p.blob + hdr->off_items);
-    const unsigned char* const seq1g = p.blob + hdr->off_seq1;
     const uint32_t bar = smem_u32(mbar);
     uint32_t parity = 0;
-
-    // Sequences longer than Seq1 have no candidates: (INT_MIN, 0, 0) as the reference's
-    // untouched `max` (cudaFunctions.cu:113,170-172).
-    if (p.write_empty) {
-        for (uint32_t s = blockIdx.x * kThreads + tid; s < hdr->nseq; s += gridDim.x * kThreads)
-            if (seqtab[s].ntiles == 0) p.out[s] = make_int4(INT_MIN, 0, 0, 0);
-    }
+    uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
 
     if (tid == 0) {
         mbar_init(bar, 1);
         mbar_fence_init();
+        ctl[3] = 0u;  // abort flag
     }
     __syncthreads();
-    // Pair-value table -> shared memory, once per CTA.
-    if (tid == 0) {
-        mbar_expect_tx(bar, kLutBytes);
-        bulk_g2s(smem_u32(lut_b), p.blob + hdr->off_lut, kLutBytes, bar);
+
+    if (kFabric && p.world > 1) {
+        if (p.rank == 0) {
+            // ---- broadcast, fused with scoring: each CTA pushes its share of chunks, then scores
+            const uint32_t total = hdr->total_bytes, chunk = hdr->chunk_bytes, nchunks = hdr->nchunks;
+            for (uint32_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
+                const uint32_t base = c * chunk;
+                const uint32_t n16 = (min(chunk, total - base) + 15u) >> 4;
+                const int4* src = reinterpret_cast<const int4*>(p.blob + base);
+                if (p.use_mc) {
+                    int4* dst = reinterpret_cast<int4*>(p.mc + p.off_blob + base);
+                    for (uint32_t i = tid; i < n16; i += kThreads) multimem_st_v4(dst + i, src[i]);
+                } else {
+                    for (uint32_t i = tid; i < n16; i += kThreads) {
+                        const int4 v = src[i];
+                        for (uint32_t r = 1; r < p.world; ++r)
+                            reinterpret_cast<int4*>(p.peer[r] + p.off_blob + base)[i] = v;
+                    }
+                }
+                __syncthreads();
+                if (tid == 0) {
+                    __threadfence_system();
+                    for (uint32_t r = 1; r < p.world; ++r)
+                        st_release_sys(reinterpret_cast<uint32_t*>(p.peer[r] + p.off_ctrl) + kCtlFlags + c, p.epoch);
+                }
+            }
+        } else {
+            // ---- wait for the chunks that hold header, table, Seq1, descriptors and items
+            if (tid == 0) {
+                bool ok = wait_flag(my_ctl + kCtlFlags, p.epoch, p.timeout_ns);
+                if (ok) {
+                    const uint32_t npre = (hdr->off_seq2 + hdr->chunk_bytes - 1u) / hdr->chunk_bytes;
+                    for (uint32_t c = 1; ok && c < npre; ++c) ok = wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns);
+                }
+                if (!ok) {
+                    ctl[3] = 1u;
+                    atomicExch(my_ctl + kCtlError, 1u);
+                }
+                fence_proxy_async();
+            }
+            __syncthreads();
+        }
     }
-    mbar_wait(bar, parity);
-    parity ^= 1u;
+    const bool dead_on_arrival = kFabric && ctl[3] != 0u;
+
+    const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + (dead_on_arrival ? 0u : hdr->off_seqtab));
+    const sa_item* const items = reinterpret_cast<const sa_item*>(p.blob + (dead_on_arrival ? 0u : hdr->off_items));
+    const unsigned char* const seq1g = p.blob + (dead_on_arrival ? 0u : hdr->off_seq1);
+    const uint32_t item_begin = kFabric ? (dead_on_arrival ? 0u : hdr->rank_first_item[p.rank]) : p.item_begin;
+    const uint32_t item_end = kFabric ? (dead_on_arrival ? 0u : hdr->rank_first_item[p.rank + 1]) : p.item_end;
+    int4* const out = kFabric ? reinterpret_cast<int4*>(p.peer[0] + p.off_out) : p.out;
+
+    // Sequences longer than Seq1 have no candidates: (INT_MIN, 0, 0) as the reference's
+    // untouched `max` (cudaFunctions.cu:113,170-172).
+    if (p.write_empty && !dead_on_arrival) {
+        for (uint32_t s = blockIdx.x * kThreads + tid; s < hdr->nseq; s += gridDim.x * kThreads)
+            if (seqtab[s].ntiles == 0) out[s] = make_int4(INT_MIN, 0, 0, 0);
+    }
+    // Pair-value table -> shared memory, once per CTA.
+    if (!dead_on_arrival) {
+        if (tid == 0) {
+            mbar_expect_tx(bar, kLutBytes);
+            bulk_g2s(smem_u32(lut_b), p.blob + hdr->off_lut, kLutBytes, bar);
+        }
+        mbar_wait(bar, parity);
+        parity ^= 1u;
+    }
 
     for (;;) {
-        if (tid == 0) ctl[0] = p.item_begin + atomicAdd(&p.ctrl[0], 1u);
+        if (tid == 0) {
+            const uint32_t it = item_begin + atomicAdd(&my_ctl[kCtlNext], 1u);
+            if (kFabric && p.rank != 0 && it < item_end) {  // this sequence's letters may still be in flight
+                const sa_seq_desc d = seqtab[items[it].seq];
+                const uint32_t bytes = ((uint32_t)d.crow * ((uint32_t)kWarps >> d.wd_log2) + 15u) & ~15u;
+                const uint32_t c0 = d.off / hdr->chunk_bytes, c1 = (d.off + bytes - 1u) / hdr->chunk_bytes;
+                bool ok = true;
+                for (uint32_t c = c0; ok && c <= c1; ++c) ok = wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns);
+                if (!ok) {
+                    ctl[3] = 1u;
+                    atomicExch(my_ctl + kCtlError, 1u);
+                }
+                fence_proxy_async();
+            }
+            ctl[0] = it;
+        }
         __syncthreads();  // also: every read of s2/win/csum of the previous item is done
         const uint32_t item = ctl[0];
-        if (item >= p.item_end) break;
+        if (item >= item_end || (kFabric && ctl[3] != 0u)) break;
 
         const uint32_t seq = items[item].seq, tile = items[item].tile;
         const sa_seq_desc sd = seqtab[seq];
         const uint32_t wd_log2 = sd.wd_log2, wd = 1u << wd_log2, wr = (uint32_t)kWarps >> wd_log2;
         const uint32_t crow = sd.crow, rows_padded = crow * wr;
         const uint32_t tn = (uint32_t)SA_DIAG_PER_WARP << wd_log2, n0 = tile * tn;
+
+        unsigned long long* const keyp =
+            (kFabric ? reinterpret_cast<unsigned long long*>(p.peer[sd.home] + p.off_key) : p.key) + seq;
+        unsigned int* const cntp = (kFabric ? reinterpret_cast<unsigned int*>(p.peer[sd.home] + p.off_cnt) : p.cnt) + seq;
 
         if (tid == 0) {
             const uint32_t s2_bytes = (rows_padded + 15u) & ~15u;
@@ -230,9 +352,16 @@ __global__ void __launch_bounds__(kThreads, 2) sa_score_kernel(const KParams p) 
 #pragma unroll
             for (int o = 8; o > 0; o >>= 1) v = umax64(v, __shfl_xor_sync(0xFFFFFFFFu, v, o));
             if (lane == 0) {
-                atomicMax(&p.key[seq], v);
-                __threadfence();
-                const unsigned int old = atomicAdd(&p.cnt[seq], 1u);
+                unsigned int old;
+                if (kFabric) {
+                    atomicMax_system(keyp, v);
+                    __threadfence_system();
+                    old = atomicAdd_system(cntp, 1u);
+                } else {
+                    atomicMax(keyp, v);
+                    __threadfence();
+                    old = atomicAdd(cntp, 1u);
+                }
                 ctl[1] = (old + 1u == sd.ntiles) ? 1u : 0u;
                 ctl[2] = 0x7FFFFFFFu;
             }
@@ -242,8 +371,13 @@ __global__ void __launch_bounds__(kThreads, 2) sa_score_kernel(const KParams p) 
         // ---- last tile of this sequence: find the first k on the winning diagonal
         if (ctl[1]) {
             if (tid == 0) {
-                __threadfence();
-                red[0] = atomicMax(&p.key[seq], 0ull);  // coherent read of the final key
+                if (kFabric) {
+                    __threadfence_system();
+                    red[0] = atomicMax_system(keyp, 0ull);  // coherent read of the final key
+                } else {
+                    __threadfence();
+                    red[0] = atomicMax(keyp, 0ull);
+                }
             }
             __syncthreads();
             const unsigned long long fk = red[0];
@@ -299,23 +433,43 @@ __global__ void __launch_bounds__(kThreads, 2) sa_score_kernel(const KParams p) 
                 }
             }
             if (tid == 0) {
-                p.out[seq] = make_int4(bestv, (int)nwin, kres, 0);
-                p.key[seq] = 0ull;  // leave the scratch zeroed for the next launch
-                p.cnt[seq] = 0u;
+                out[seq] = make_int4(bestv, (int)nwin, kres, 0);
+                *keyp = 0ull;  // leave the scratch zeroed for the next launch
+                *cntp = 0u;
             }
         }
     }
 
     // Last CTA out re-arms the work queue for the next launch.
     if (tid == 0) {
-        __threadfence();
-        const unsigned int done = atomicAdd(&p.ctrl[1], 1u);
+        if (kFabric) __threadfence_system(); else __threadfence();
+        const unsigned int done = atomicAdd(&my_ctl[kCtlCtasDone], 1u);
         if (done + 1u == gridDim.x) {
-            p.ctrl[0] = 0u;
-            p.ctrl[1] = 0u;
+            my_ctl[kCtlNext] = 0u;
+            my_ctl[kCtlCtasDone] = 0u;
+            if (kFabric && p.world > 1) {
+                // Gather: everything this rank produced is already in rank 0's table; tell rank 0.
+                uint32_t* const arrived = reinterpret_cast<uint32_t*>(p.peer[0] + p.off_ctrl) + kCtlRanksDone;
+                __threadfence_system();
+                atomicAdd_system(arrived, 1u);
+                if (p.rank == 0) {  // the launch on rank 0 ends only when every rank has delivered
+                    const unsigned long long t0 = global_ns();
+                    while (ld_acquire_sys(arrived) < p.world) {
+                        __nanosleep(128);
+                        if (global_ns() - t0 > p.timeout_ns) {
+                            atomicExch(my_ctl + kCtlError, 2u);
+                            break;
+                        }
+                    }
+                    *arrived = 0u;
+                }
+            }
         }
     }
 }
+
+__global__ void __launch_bounds__(kThreads, 2) sa_score_kernel(const KParams p) { score_body<false>(p); }
+__global__ void __launch_bounds__(kThreads, 2) sa_score_fabric_kernel(const KParams p) { score_body<true>(p); }
 
 // ------------------------------------------------------------------ host side
 
@@ -326,6 +480,7 @@ struct DeviceInfo {
     int sm_count = 0;
     int max_optin_smem = 0;
     int smem_set = 0;
+    int smem_fabric_set = 0;
 };
 std::mutex g_mu;
 DeviceInfo g_dev[64];
@@ -488,6 +643,100 @@ int sa_cuda_solve_problem(const sa_problem* prob, int32_t* out, int device) {
 }
 
 uint64_t sa_cuda_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+// ------------------------------------------------------------------ fabric (multi-GPU) launch
+
+int sa_fabric_layout(uint32_t max_seq, size_t max_blob_bytes, sa_fabric_layout_t* out) {
+    if (!out || max_seq == 0) {
+        sa_set_last_error("sa_fabric_layout: bad argument");
+        return SA_ERR_ARG;
+    }
+    size_t off = 0;
+    out->off_ctrl = (uint32_t)off;
+    off += round_up_sz((kCtlFlags + kMaxChunks) * 4, 256);
+    out->off_key = (uint32_t)off;
+    off += key_bytes(max_seq);
+    out->off_cnt = (uint32_t)off;
+    off += cnt_bytes(max_seq);
+    out->off_out = (uint32_t)off;
+    off += round_up_sz((size_t)max_seq * 16, 256);
+    out->off_blob = (uint32_t)off;
+    off += round_up_sz(max_blob_bytes, 256);
+    if (off >= 0xFFFFFFFFull) {
+        sa_set_last_error("sa_fabric_layout: symmetric buffer would exceed 4 GiB");
+        return SA_ERR_UNSUPPORTED;
+    }
+    out->total_bytes = off;
+    out->max_seq = max_seq;
+    out->max_blob_bytes = max_blob_bytes;
+    return SA_OK;
+}
+
+int sa_cuda_fabric_solve(const sa_fabric_desc* f, const sa_blob_header* header, void* stream) {
+    if (!f || f->world < 1 || f->world > SA_MAX_WORLD || f->rank >= f->world) {
+        sa_set_last_error("sa_cuda_fabric_solve: bad descriptor");
+        return SA_ERR_ARG;
+    }
+    if (f->rank == 0) {
+        if (!header || header->magic != SA_BLOB_MAGIC || header->version != SA_BLOB_VERSION) {
+            sa_set_last_error("sa_cuda_fabric_solve: rank 0 must pass the host copy of the blob header");
+            return SA_ERR_ARG;
+        }
+        if (header->world != f->world) {
+            sa_set_last_error("sa_cuda_fabric_solve: blob was planned for a different number of GPUs");
+            return SA_ERR_ARG;
+        }
+        if (header->nseq > f->layout.max_seq || header->total_bytes > f->layout.max_blob_bytes ||
+            header->nchunks > kMaxChunks || header->max_rows_padded > SA_GPU_MAX_SEQ2 + 128u) {
+            sa_set_last_error("sa_cuda_fabric_solve: problem exceeds the capacity this fabric was created with");
+            return SA_ERR_TOO_LARGE;
+        }
+    }
+    int dev = 0;
+    SA_CUDA_TRY(cudaGetDevice(&dev));
+    DeviceInfo* di = nullptr;
+    int rc = device_info(dev, &di);
+    if (rc != SA_OK) return rc;
+
+    KParams p{};
+    for (uint32_t r = 0; r < f->world; ++r) {
+        if (!f->peer_base[r]) {
+            sa_set_last_error("sa_cuda_fabric_solve: missing peer mapping");
+            return SA_ERR_ARG;
+        }
+        p.peer[r] = static_cast<unsigned char*>(f->peer_base[r]);
+    }
+    p.mc = static_cast<unsigned char*>(f->mc_base);
+    p.use_mc = (f->use_multicast && f->mc_base) ? 1u : 0u;
+    p.rank = f->rank;
+    p.world = f->world;
+    p.epoch = f->epoch;
+    p.off_ctrl = f->layout.off_ctrl;
+    p.off_key = f->layout.off_key;
+    p.off_cnt = f->layout.off_cnt;
+    p.off_out = f->layout.off_out;
+    p.off_blob = f->layout.off_blob;
+    p.timeout_ns = (unsigned long long)(f->timeout_ms ? f->timeout_ms : 10000u) * 1000000ull;
+    p.blob = p.peer[f->rank] + p.off_blob;
+    p.write_empty = f->rank == 0 ? 1u : 0u;
+    // Ranks other than 0 know nothing about the problem at launch time, so every rank launches the
+    // same input-independent shape: full persistent grid, shared memory for the largest sequence.
+    p.s2_cap = (SA_GPU_MAX_SEQ2 + 128u + 15u) & ~15u;
+    p.win_cap = (SA_GPU_MAX_SEQ2 + 128u + 4096u + 16u + 15u) & ~15u;
+    const uint32_t smem = smem_bytes_for(p.s2_cap, p.win_cap);
+    {
+        std::lock_guard<std::mutex> lock(g_mu);
+        if ((int)smem > di->smem_fabric_set) {
+            SA_CUDA_TRY(cudaFuncSetAttribute(sa_score_fabric_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            di->smem_fabric_set = (int)smem;
+        }
+    }
+    const uint32_t grid = (uint32_t)di->sm_count * 2u;
+    sa_score_fabric_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+    SA_CUDA_TRY(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return SA_OK;
+}
 
 // ---------------------------------------------------------------------------------------
 // Fixed-capacity variant for callers that must not allocate device memory.

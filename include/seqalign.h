@@ -173,6 +173,12 @@ void sa_blob_free(void* blob);
  * row-chunk / combine / packed-key / first-k logic of the GPU kernel. Used to
  * validate planner+packer without a GPU (out: int32[4*nseq] = score,n,k,0). */
 int sa_blob_execute_cpu(const void* blob, size_t blob_bytes, int32_t* out4);
+/* The two halves of the walk, for the multi-process CPU configuration (BASELINE.json
+ * configs[0]): each rank scores its own item range into packed keys (keys[nseq], max-merged,
+ * start from zero), the keys are max-reduced across ranks, then rank 0 finalises. */
+int sa_blob_score_items_cpu(const void* blob, size_t blob_bytes, uint32_t first_item,
+                            uint32_t last_item, uint64_t* keys);
+int sa_blob_finalize_cpu(const void* blob, size_t blob_bytes, const uint64_t* keys, int32_t* out4);
 
 /* The work partition over `world` GPUs (new-build analogue of main.c:110-121) is part
  * of the plan: whole sequences are dealt to the least-loaded rank, costliest first;
@@ -228,6 +234,47 @@ int sa_cuda_solve_problem(const sa_problem* p, int32_t* out, int device);
  *    its own scratch through sa_cuda_solve_blob. */
 int sa_cuda_solve_blob_noalloc(const void* d_blob, const sa_blob_header* header, int32_t* d_out,
                                void* stream);
+
+/* ------------------------------------------------------------------- fabric */
+
+/* Multi-GPU execution: one process per GPU, every process launches ONE kernel per solve.
+ * Replaces the reference's MPI data path (main.c:149-152 Bcast x4, :174 Scatter, :195-197
+ * Gather x3): rank 0's kernel broadcasts the packed blob into every peer's buffer (NVLS
+ * multicast store, or per-peer P2P stores) while it already scores; peers score as soon as
+ * the chunks they need have landed; per-sequence argmax keys are reduced with system-scope
+ * atomics in the home rank's memory; results are written straight into rank 0's table and the
+ * last CTA of each rank signals rank 0. The host only exchanges buffer mappings once
+ * (bootstrap) — no MPI/NCCL call on the data path. */
+#define SA_FABRIC_MAX_CHUNKS 1024u
+
+typedef struct sa_fabric_layout_t {
+    uint32_t off_ctrl, off_key, off_cnt, off_out, off_blob;
+    uint32_t max_seq;
+    uint64_t max_blob_bytes;
+    uint64_t total_bytes; /* size of the symmetric buffer every rank must allocate */
+} sa_fabric_layout_t;
+
+/* Offsets of the regions inside each rank's symmetric buffer. */
+int sa_fabric_layout(uint32_t max_seq, size_t max_blob_bytes, sa_fabric_layout_t* out);
+
+typedef struct sa_fabric_desc {
+    uint32_t rank, world;
+    uint32_t epoch;         /* 1, 2, 3, ... — the same on every rank for the same solve      */
+    uint32_t use_multicast; /* broadcast with multimem.st through mc_base (else P2P stores)  */
+    uint32_t timeout_ms;    /* bound on every cross-GPU wait (0 = 10 s)                       */
+    uint32_t pad0;
+    void* peer_base[SA_MAX_WORLD]; /* rank r's symmetric buffer as mapped in THIS process     */
+    void* mc_base;                 /* multicast mapping of the buffer, or NULL                */
+    sa_fabric_layout_t layout;
+} sa_fabric_desc;
+
+/* Launch this rank's share of a solve on the current device/stream. Rank 0 must have copied the
+ * blob (planned with world == f->world) to peer_base[0] + layout.off_blob and passes the host
+ * copy of its header; other ranks pass NULL. The symmetric buffers must be zero before the
+ * first solve. After the stream has drained, rank 0 finds int32[4*nseq] at
+ * peer_base[0] + layout.off_out, and every rank finds a non-zero word at
+ * peer_base[rank] + layout.off_ctrl + 12 if one of its waits timed out. */
+int sa_cuda_fabric_solve(const sa_fabric_desc* f, const sa_blob_header* header, void* stream);
 
 /* Number of kernel launches issued by this library in this process. */
 uint64_t sa_cuda_launch_count(void);

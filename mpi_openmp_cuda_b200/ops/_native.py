@@ -85,6 +85,8 @@ def core() -> C.CDLL:
     lib.sa_format.restype = sz
     lib.sa_plan_pack_into.argtypes = [vp, C.c_int, C.c_void_p, sz, C.POINTER(sz)]
     lib.sa_blob_execute_cpu.argtypes = [C.c_void_p, sz, i32p]
+    lib.sa_blob_score_items_cpu.argtypes = [C.c_void_p, sz, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
+    lib.sa_blob_finalize_cpu.argtypes = [C.c_void_p, sz, C.POINTER(C.c_uint64), i32p]
     return lib
 
 

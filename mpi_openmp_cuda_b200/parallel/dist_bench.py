@@ -1,0 +1,132 @@
+"""Multi-GPU timing for bench.py (one process per GPU under torchrun).
+
+Device-timed with CUDA events per rank, max over ranks per step. Rank 0's launch ends only when
+every rank has delivered its results into rank 0's table, so its events already span broadcast +
+scoring + gather; the max over ranks is still taken, as the contract asks.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from ..ops import plan
+from ..ops.score import launch_count
+from ..utils.clocks import ClockSampler
+from ..utils.timing import L2Flusher
+from .dist_solver import DistributedSolver
+from .fabric import Fabric, init_distributed
+
+
+class _Align:
+    """Device-side alignment of the ranks before a timed step: a tiny all-reduce enqueued on the
+    stream (no host synchronisation), so that every GPU reaches the timed launch within
+    microseconds of the others and host launch skew is not billed to the solve."""
+
+    def __init__(self):
+        self.t = torch.zeros(1, device="cuda")
+
+    def __call__(self):
+        dist.all_reduce(self.t)
+
+
+def _max_over_ranks(ms: list[float]) -> list[float]:
+    t = torch.tensor(ms, dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(x) for x in t.cpu()]
+
+
+def time_ours_distributed(problem, steps: int, warmup: int):
+    rank, world, local = init_distributed("nccl")
+    # capacity handshake (bootstrap, outside any timed region): only rank 0 knows the problem
+    need = torch.zeros(2, dtype=torch.int64, device="cuda")
+    if rank == 0:
+        need[0] = plan.blob_size(problem, world)
+        need[1] = problem.nseq
+    dist.broadcast(need, 0)
+    fabric = Fabric(max_seq=max(int(need[1].item()), 64), max_blob_bytes=int(need[0].item()) + (1 << 20))
+    solver = DistributedSolver(fabric)
+    flusher = L2Flusher(fabric.device)
+    blob = solver.pack(problem) if rank == 0 else None
+    nseq = int(need[1].item())
+    align = _Align()
+
+    def step_kernel_only():
+        # blob already resident in rank 0's symmetric buffer: launch only
+        if rank == 0:
+            fabric.launch(blob.header)
+        else:
+            fabric.launch(None)
+
+    # first solve (uploads the blob on rank 0) + correctness snapshot
+    solver.launch_packed(blob)
+    res = solver.fetch(nseq)
+    res = res.copy() if rank == 0 else None
+    solver.check()
+
+    for _ in range(warmup):
+        flusher.flush()
+        align()
+        step_kernel_only()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local).start()
+    l0 = launch_count()
+    kernel_ms = []
+    dist.barrier()
+    torch.cuda.synchronize()
+    for _ in range(steps):
+        flusher.flush()
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        align()
+        e0.record()
+        step_kernel_only()
+        e1.record()
+        e1.synchronize()
+        kernel_ms.append(e0.elapsed_time(e1))
+    launches = launch_count() - l0
+    torch.cuda.synchronize()
+    solver.check()
+
+    def e2e_step(prepacked: bool) -> float:
+        flusher.flush()
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        align()
+        e0.record()
+        if rank == 0:
+            b = blob if prepacked else solver.pack(problem)
+            solver.launch_packed(b)
+            solver.fetch(nseq)
+        else:
+            solver.launch_packed(None)
+            solver.fetch(0)
+        e1.record()
+        e1.synchronize()
+        return e0.elapsed_time(e1)
+
+    for _ in range(warmup):
+        e2e_step(False)
+    e2e_ms = [e2e_step(False) for _ in range(steps)]
+    pre_ms = [e2e_step(True) for _ in range(steps)]
+    clocks = sampler.stop()
+    solver.check()
+    kernel_ms, e2e_ms, pre_ms = _max_over_ranks(kernel_ms), _max_over_ranks(e2e_ms), _max_over_ranks(pre_ms)
+    total_launches = torch.tensor([launches], dtype=torch.int64, device="cuda")
+    dist.all_reduce(total_launches)
+    dist.barrier()
+    if rank != 0:
+        dist.destroy_process_group()
+        return None
+    final = solver.fetch(nseq).copy()
+    assert np.array_equal(final, res), "results changed between steps"
+    out = {
+        "kernel_ms": kernel_ms, "e2e_ms": e2e_ms, "e2e_prepacked_ms": pre_ms, "launches": int(total_launches.item()),
+        "clocks": clocks, "h2d": blob.nbytes, "d2h": nseq * 16, "result": res,
+        "padded_cells": int(blob.header.padded_cells), "nitems": blob.nitems,
+        "fabric": {"multicast": fabric.use_multicast, "world": world},
+    }
+    dist.destroy_process_group()
+    return out

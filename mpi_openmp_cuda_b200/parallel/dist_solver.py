@@ -1,0 +1,80 @@
+"""Multi-GPU solver: the reference's master/worker run (main.c:46-244) as one kernel per GPU.
+
+Rank 0 is the only rank that ever sees the problem (as in the reference, where only the root
+reads stdin): it plans for `world` GPUs, packs, copies the blob into its own symmetric buffer
+and launches. Every other rank just launches — its kernel receives the data over NVLink from
+rank 0's kernel, scores its share and writes results into rank 0's table.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from ..ops import plan
+from .fabric import Fabric
+
+
+class DistributedSolver:
+    def __init__(self, fabric: Fabric):
+        self.fabric = fabric
+        self._pin_in = None
+        self._pin_out = None
+
+    @property
+    def rank(self) -> int:
+        return self.fabric.rank
+
+    def _pinned_in(self, nbytes: int) -> torch.Tensor:
+        if self._pin_in is None or self._pin_in.numel() < nbytes:
+            self._pin_in = torch.empty(max(nbytes, 1 << 16), dtype=torch.uint8, pin_memory=True)
+        return self._pin_in
+
+    def pack(self, problem) -> plan.PackedBlob:
+        need = plan.blob_size(problem, self.fabric.world)
+        return plan.plan_pack(problem, self.fabric.world, out=self._pinned_in(need))
+
+    def launch_packed(self, blob: plan.PackedBlob | None) -> None:
+        """All ranks call this once per solve; only rank 0 passes a blob."""
+        f = self.fabric
+        if f.rank == 0:
+            if blob is None:
+                raise ValueError("rank 0 must provide the packed problem")
+            if blob.nbytes > f.layout.max_blob_bytes or blob.nseq > f.layout.max_seq:
+                raise ValueError("problem exceeds the fabric's capacity; create the Fabric with larger limits")
+            src = blob.data if isinstance(blob.data, torch.Tensor) else torch.from_numpy(blob.data)
+            f.blob_region[: blob.nbytes].copy_(src[: blob.nbytes], non_blocking=True)
+            f.launch(blob.header)
+        else:
+            f.launch(None)
+
+    def fetch(self, nseq: int, sync: bool = True) -> np.ndarray | None:
+        """Rank 0: D2H of the result table (after its kernel, which ends only when all ranks delivered)."""
+        f = self.fabric
+        if f.rank != 0:
+            if sync:
+                torch.cuda.current_stream().synchronize()
+            return None
+        if self._pin_out is None or self._pin_out.shape[0] < nseq:
+            self._pin_out = torch.empty((max(nseq, 64), 4), dtype=torch.int32, pin_memory=True)
+        self._pin_out[:nseq].copy_(f.out_region(nseq), non_blocking=True)
+        if sync:
+            torch.cuda.current_stream().synchronize()
+        return self._pin_out[:nseq, :3].numpy()
+
+    def check(self) -> None:
+        err = self.fabric.error_word()
+        if err:
+            raise RuntimeError(f"fabric wait timed out on rank {self.rank} (code {err}): a peer GPU did not deliver")
+
+    def solve(self, problem=None) -> np.ndarray | None:
+        """Collective: every rank calls solve(); rank 0 passes the problem and gets int32[nseq,3]."""
+        if self.rank == 0:
+            blob = self.pack(problem)
+            self.launch_packed(blob)
+            res = self.fetch(blob.nseq)
+            self.check()
+            return res.copy()
+        self.launch_packed(None)
+        self.fetch(0)
+        self.check()
+        return None

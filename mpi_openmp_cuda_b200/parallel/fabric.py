@@ -1,0 +1,111 @@
+"""Bootstrap of the GPU fabric: one process per GPU, a symmetric buffer per rank mapped into
+every peer (NVLink 5 / NVSwitch), plus the NVLS multicast alias when the platform has one.
+
+torch.distributed (+ torch symmetric memory) is used ONLY here, to exchange the mappings once.
+The data path — broadcast of the input, argmax reduce, gather of results — runs inside
+`sa_score_fabric_kernel` (csrc/cuda/align_kernel.cu) and replaces the reference's
+MPI_Bcast/Scatter/Gather (main.c:149-152,174,195-197).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _native as N
+
+
+class FabricLayout(C.Structure):
+    _fields_ = [("off_ctrl", C.c_uint32), ("off_key", C.c_uint32), ("off_cnt", C.c_uint32),
+                ("off_out", C.c_uint32), ("off_blob", C.c_uint32), ("max_seq", C.c_uint32),
+                ("max_blob_bytes", C.c_uint64), ("total_bytes", C.c_uint64)]
+
+
+class FabricDesc(C.Structure):
+    _fields_ = [("rank", C.c_uint32), ("world", C.c_uint32), ("epoch", C.c_uint32), ("use_multicast", C.c_uint32),
+                ("timeout_ms", C.c_uint32), ("pad0", C.c_uint32),
+                ("peer_base", C.c_void_p * N.SA_MAX_WORLD), ("mc_base", C.c_void_p), ("layout", FabricLayout)]
+
+
+def init_distributed(backend: str | None = None) -> tuple[int, int, int]:
+    """Join the job described by RANK / WORLD_SIZE / LOCAL_RANK / MASTER_* (torchrun or our launcher)."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", str(rank)))
+    if backend is None:
+        backend = "nccl" if torch.cuda.is_available() else "gloo"
+    if backend == "nccl":
+        torch.cuda.set_device(local)
+    if not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29531")
+        kw = {"device_id": torch.device("cuda", local)} if backend == "nccl" else {}
+        dist.init_process_group(backend, rank=rank, world_size=world, **kw)
+    return rank, world, local
+
+
+class Fabric:
+    """Symmetric buffer + peer mappings for `world` GPUs of one node."""
+
+    def __init__(self, max_seq: int = 1 << 16, max_blob_bytes: int = 96 << 20, use_multicast: bool | None = None,
+                 timeout_ms: int = 10000, group=None):
+        import torch.distributed._symmetric_memory as symm
+
+        if not dist.is_initialized():
+            raise RuntimeError("Fabric needs torch.distributed (see init_distributed)")
+        self.group = group or dist.group.WORLD
+        self.rank, self.world = dist.get_rank(self.group), dist.get_world_size(self.group)
+        if self.world > N.SA_MAX_WORLD:
+            raise ValueError(f"at most {N.SA_MAX_WORLD} GPUs")
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self.lib = N.cuda()
+        self.lib.sa_fabric_layout.argtypes = [C.c_uint32, C.c_size_t, C.POINTER(FabricLayout)]
+        self.lib.sa_cuda_fabric_solve.argtypes = [C.POINTER(FabricDesc), C.POINTER(N.BlobHeader), C.c_void_p]
+        self.layout = FabricLayout()
+        N.check(self.lib.sa_fabric_layout(max_seq, max_blob_bytes, C.byref(self.layout)))
+        self.buf = symm.empty(int(self.layout.total_bytes), dtype=torch.uint8, device=self.device)
+        self.buf.zero_()
+        torch.cuda.synchronize()
+        self.hdl = symm.rendezvous(self.buf, self.group)
+        self.peer_ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        mc = int(self.hdl.multicast_ptr) if self.hdl.has_multicast_support else 0
+        env = os.environ.get("SA_FABRIC_MULTICAST")
+        if use_multicast is None:
+            use_multicast = (env != "0") if env is not None else True
+        self.mc_ptr = mc
+        self.use_multicast = bool(use_multicast and mc != 0 and self.world > 1)
+        self.timeout_ms = timeout_ms
+        self.epoch = 0
+        self.hdl.barrier()  # every rank's buffer is zeroed and mapped before anyone launches
+
+    # views into this rank's own buffer
+    def region(self, off: int, nbytes: int) -> torch.Tensor:
+        return self.buf[off : off + nbytes]
+
+    @property
+    def blob_region(self) -> torch.Tensor:
+        return self.buf[self.layout.off_blob : self.layout.off_blob + self.layout.max_blob_bytes]
+
+    def out_region(self, nseq: int) -> torch.Tensor:
+        return self.buf[self.layout.off_out : self.layout.off_out + 16 * nseq].view(torch.int32).view(nseq, 4)
+
+    def error_word(self) -> int:
+        return int(self.buf[self.layout.off_ctrl + 12 : self.layout.off_ctrl + 16].view(torch.int32).item())
+
+    def launch(self, header: N.BlobHeader | None) -> None:
+        """Enqueue this rank's kernel of the next solve on the current stream."""
+        self.epoch += 1
+        d = FabricDesc()
+        d.rank, d.world, d.epoch = self.rank, self.world, self.epoch
+        d.use_multicast = 1 if self.use_multicast else 0
+        d.timeout_ms = self.timeout_ms
+        for r in range(self.world):
+            d.peer_base[r] = self.peer_ptrs[r]
+        d.mc_base = self.mc_ptr or None
+        d.layout = self.layout
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        hdr = C.byref(header) if header is not None else None
+        with torch.cuda.device(self.device):
+            N.check(self.lib.sa_cuda_fabric_solve(C.byref(d), hdr, C.c_void_p(stream)))

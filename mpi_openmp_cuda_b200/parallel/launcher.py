@@ -1,0 +1,95 @@
+"""`python -m mpi_openmp_cuda_b200.parallel.launcher --gpus N < input` — the multi-GPU (or, with
+--cpu, multi-process CPU) form of `./final`: same stdin, same stdout bytes.
+
+Analogue of `mpiexec -np N ./final` (makefile:11): spawns one worker process per GPU on this
+node (127.0.0.1 rendezvous), feeds stdin to rank 0 only, prints rank 0's result lines.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import socket
+import subprocess
+import sys
+import time
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def worker(cpu: bool, timing_path: str | None) -> int:
+    import torch.distributed as dist
+
+    from .. import Problem, format_results
+    from .fabric import init_distributed
+
+    # stdout carries the result lines and nothing else (byte parity with the reference), but
+    # libraries such as NCCL may print banners to fd 1: park the real stdout, point fd 1 at stderr.
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    t0 = time.perf_counter()
+    rank, world, local = init_distributed("gloo" if cpu else "nccl")
+    problem = Problem.parse(sys.stdin.buffer.read()) if rank == 0 else None
+    t1 = time.perf_counter()
+    if cpu:
+        from .cpu_world import solve_cpu_world
+
+        res = solve_cpu_world(problem)
+    else:
+        from .dist_solver import DistributedSolver
+        from .fabric import Fabric
+
+        solver = DistributedSolver(Fabric())
+        res = solver.solve(problem)
+    t2 = time.perf_counter()
+    if rank == 0:
+        data = format_results(res)
+        while data:
+            data = data[os.write(real_stdout, data):]
+        if timing_path:
+            with open(timing_path, "w") as f:
+                json.dump({"engine": "cpu-world" if cpu else "gpu-fabric", "world": world, "nseq": problem.nseq,
+                           "candidates": problem.candidates(), "bootstrap_parse_s": t1 - t0, "solve_s": t2 - t1}, f)
+    dist.barrier()
+    dist.destroy_process_group()
+    return 0
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1, help="number of worker processes (one per GPU)")
+    ap.add_argument("--cpu", action="store_true", help="CPU world: gloo + the CPU walk of the kernel logic")
+    ap.add_argument("--timing-json", default=None)
+    ap.add_argument("--worker", action="store_true", help=argparse.SUPPRESS)
+    a = ap.parse_args()
+    if a.worker:
+        return worker(a.cpu, a.timing_json)
+    port = _free_port()
+    procs = []
+    for r in range(a.gpus):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(a.gpus), LOCAL_RANK=str(r),
+                   MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        cmd = [sys.executable, "-m", "mpi_openmp_cuda_b200.parallel.launcher", "--worker", "--gpus", str(a.gpus)]
+        if a.cpu:
+            cmd.append("--cpu")
+        if a.timing_json:
+            cmd += ["--timing-json", a.timing_json]
+        procs.append(subprocess.Popen(cmd, env=env, stdin=None if r == 0 else subprocess.DEVNULL,
+                                      stdout=None if r == 0 else subprocess.DEVNULL))
+    rc = 0
+    for p in procs:
+        code = p.wait()
+        if code != 0 and rc == 0:
+            rc = code
+            for q in procs:  # a failed rank must not leave the others waiting
+                if q.poll() is None:
+                    q.kill()
+    return rc
+
+
+if __name__ == "__main__":
+    sys.exit(main())
