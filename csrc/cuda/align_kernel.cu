@@ -55,11 +55,15 @@ struct KParams {
     unsigned char* mc;                  // NVLS multicast alias of the same buffer, or null
     uint32_t off_ctrl, off_key, off_cnt, off_out, off_blob;
     unsigned long long timeout_ns;
+    uint32_t timeline;  // 1: record the globaltimer timeline in the control block
 };
 
 // Words of the control block at the start of every rank's symmetric buffer.
 constexpr uint32_t kCtlNext = 0, kCtlCtasDone = 1, kCtlRanksDone = 2, kCtlError = 3, kCtlFlags = 64;
 constexpr uint32_t kMaxChunks = SA_FABRIC_MAX_CHUNKS;
+// Optional timeline (globaltimer ns) in control words 16..31 as five 64-bit slots:
+// 0 earliest CTA start, 1 prefix ready (latest), 2 last item finished, 3 arrival sent, 4 all arrived.
+constexpr uint32_t kCtlTimes = 16;
 
 // ------------------------------------------------------------------ PTX helpers
 
@@ -164,6 +168,9 @@ __device__ __forceinline__ void score_body(const KParams& p) {
     const uint32_t bar = smem_u32(mbar);
     uint32_t parity = 0;
     uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
+    unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
+    const bool timeline = kFabric && p.timeline != 0u;
+    if (timeline && tid == 0) atomicMin(&times[0], global_ns());
 
     if (tid == 0) {
         mbar_init(bar, 1);
@@ -192,7 +199,7 @@ __device__ __forceinline__ void score_body(const KParams& p) {
                 }
                 __syncthreads();
                 if (tid == 0) {
-                    __threadfence_system();
+                    // st.release.sys is cumulative over the CTA's stores ordered before it by the barrier
                     for (uint32_t r = 1; r < p.world; ++r)
                         st_release_sys(reinterpret_cast<uint32_t*>(p.peer[r] + p.off_ctrl) + kCtlFlags + c, p.epoch);
                 }
@@ -215,6 +222,7 @@ __device__ __forceinline__ void score_body(const KParams& p) {
         }
     }
     const bool dead_on_arrival = kFabric && ctl[3] != 0u;
+    if (timeline && tid == 0) atomicMax(&times[1], global_ns());
 
     const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + (dead_on_arrival ? 0u : hdr->off_seqtab));
     const sa_item* const items = reinterpret_cast<const sa_item*>(p.blob + (dead_on_arrival ? 0u : hdr->off_items));
@@ -355,7 +363,8 @@ __device__ __forceinline__ void score_body(const KParams& p) {
                 unsigned int old;
                 if (kFabric) {
                     atomicMax_system(keyp, v);
-                    __threadfence_system();
+                    // both atomics resolve in the home rank's L2; a device-scope fence orders them there
+                    if (sd.home == p.rank) __threadfence(); else __threadfence_system();
                     old = atomicAdd_system(cntp, 1u);
                 } else {
                     atomicMax(keyp, v);
@@ -442,6 +451,7 @@ __device__ __forceinline__ void score_body(const KParams& p) {
 
     // Last CTA out re-arms the work queue for the next launch.
     if (tid == 0) {
+        if (timeline) atomicMax(&times[2], global_ns());
         if (kFabric) __threadfence_system(); else __threadfence();
         const unsigned int done = atomicAdd(&my_ctl[kCtlCtasDone], 1u);
         if (done + 1u == gridDim.x) {
@@ -452,6 +462,7 @@ __device__ __forceinline__ void score_body(const KParams& p) {
                 uint32_t* const arrived = reinterpret_cast<uint32_t*>(p.peer[0] + p.off_ctrl) + kCtlRanksDone;
                 __threadfence_system();
                 atomicAdd_system(arrived, 1u);
+                if (timeline) times[3] = global_ns();
                 if (p.rank == 0) {  // the launch on rank 0 ends only when every rank has delivered
                     const unsigned long long t0 = global_ns();
                     while (ld_acquire_sys(arrived) < p.world) {
@@ -462,6 +473,7 @@ __device__ __forceinline__ void score_body(const KParams& p) {
                         }
                     }
                     *arrived = 0u;
+                    if (timeline) times[4] = global_ns();
                 }
             }
         }
@@ -717,6 +729,7 @@ int sa_cuda_fabric_solve(const sa_fabric_desc* f, const sa_blob_header* header, 
     p.off_out = f->layout.off_out;
     p.off_blob = f->layout.off_blob;
     p.timeout_ns = (unsigned long long)(f->timeout_ms ? f->timeout_ms : 10000u) * 1000000ull;
+    p.timeline = f->pad0 & 1u;
     p.blob = p.peer[f->rank] + p.off_blob;
     p.write_empty = f->rank == 0 ? 1u : 0u;
     // Ranks other than 0 know nothing about the problem at launch time, so every rank launches the

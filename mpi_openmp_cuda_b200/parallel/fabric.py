@@ -77,7 +77,18 @@ class Fabric:
         self.mc_ptr = mc
         self.use_multicast = bool(use_multicast and mc != 0 and self.world > 1)
         self.timeout_ms = timeout_ms
+        self.timeline = os.environ.get("SA_FABRIC_TIMELINE") == "1"
         self.epoch = 0
+        d = FabricDesc()
+        d.rank, d.world = self.rank, self.world
+        d.use_multicast = 1 if self.use_multicast else 0
+        d.timeout_ms = self.timeout_ms
+        d.pad0 = 1 if self.timeline else 0
+        for r in range(self.world):
+            d.peer_base[r] = self.peer_ptrs[r]
+        d.mc_base = self.mc_ptr or None
+        d.layout = self.layout
+        self._desc = d
         self.hdl.barrier()  # every rank's buffer is zeroed and mapped before anyone launches
 
     # views into this rank's own buffer
@@ -94,17 +105,21 @@ class Fabric:
     def error_word(self) -> int:
         return int(self.buf[self.layout.off_ctrl + 12 : self.layout.off_ctrl + 16].view(torch.int32).item())
 
+    def read_timeline(self) -> dict:
+        """After a synchronised launch with SA_FABRIC_TIMELINE=1: microseconds since this rank's first CTA started."""
+        t = self.buf[self.layout.off_ctrl + 64 : self.layout.off_ctrl + 104].view(torch.int64).cpu().tolist()
+        names = ["start", "prefix_ready", "items_done", "arrival_sent", "all_arrived"]
+        return {n: (None if v in (0,) else (v - t[0]) / 1e3) for n, v in zip(names, t)} | {"start_abs_ns": t[0]}
+
     def launch(self, header: N.BlobHeader | None) -> None:
         """Enqueue this rank's kernel of the next solve on the current stream."""
         self.epoch += 1
-        d = FabricDesc()
-        d.rank, d.world, d.epoch = self.rank, self.world, self.epoch
-        d.use_multicast = 1 if self.use_multicast else 0
-        d.timeout_ms = self.timeout_ms
-        for r in range(self.world):
-            d.peer_base[r] = self.peer_ptrs[r]
-        d.mc_base = self.mc_ptr or None
-        d.layout = self.layout
+        d = self._desc
+        d.epoch = self.epoch
+        if self.timeline:  # slot 0 is a running minimum: re-arm it (and the maxima) before every launch
+            t = self.buf[self.layout.off_ctrl + 64 : self.layout.off_ctrl + 128].view(torch.int64)
+            t.zero_()
+            t[0] = torch.iinfo(torch.int64).max
         stream = torch.cuda.current_stream(self.device).cuda_stream
         hdr = C.byref(header) if header is not None else None
         with torch.cuda.device(self.device):
