@@ -174,7 +174,7 @@ def run_ours(args):
         },
         "solve_ms_min": min(m["kernel_ms"]),
         "e2e": {"value": cands / (e2e * 1e-3), "unit": "candidates/s", "ms_per_step": e2e,
-                "what": "solver.solve(problem): plan+pack into pinned memory, H2D, kernel, D2H, sync",
+                "what": "AlignmentSolver.solve(problem): plan+pack into pinned memory, H2D, kernel, D2H, sync",
                 "h2d_bytes_per_step": m["h2d"], "d2h_bytes_per_step": m["d2h"],
                 "prepacked_ms_per_step": pre},
         "gpu_launches": m["launches"],

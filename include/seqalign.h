@@ -235,6 +235,24 @@ int sa_cuda_solve_problem(const sa_problem* p, int32_t* out, int device);
 int sa_cuda_solve_blob_noalloc(const void* d_blob, const sa_blob_header* header, int32_t* d_out,
                                void* stream);
 
+/* Solver session: owns a stream, pinned staging and device buffers on one GPU, all reused and
+ * only ever grown. sa_session_solve is the complete per-problem host path in one call (plan +
+ * pack into pinned memory, H2D, one launch, D2H, stream synchronise) — what
+ * send_divided_Seq2_To_Cuda (cudaFunctions.cu:178-242) does with 4+N cudaMallocs, N device
+ * synchronisations and 5 cudaFrees per call. out3: int32[3*nseq]. Not thread-safe per session. */
+typedef struct sa_session sa_session;
+int sa_session_create(int device, sa_session** out);
+void sa_session_destroy(sa_session* s);
+int sa_session_solve(sa_session* s, const sa_problem* p, int32_t* out3);
+/* Transfer policy. Blobs of at most zero_copy_max_bytes are read by the kernel in place from
+ * pinned host memory (no DMA copy; 0 = always copy, the default — measured on B200 the in-place
+ * read is 1.5-2.5x slower end to end because every CTA re-reads the table over PCIe); with direct_out != 0
+ * (default) result rows are posted by the kernel straight into pinned host memory instead of
+ * being copied back afterwards. Either way every input byte crosses PCIe once per solve. */
+void sa_session_configure(sa_session* s, size_t zero_copy_max_bytes, int direct_out);
+/* Bytes moved over PCIe by the last solve (for benchmark reporting). */
+void sa_session_last_bytes(const sa_session* s, uint64_t* h2d, uint64_t* d2h);
+
 /* ------------------------------------------------------------------- fabric */
 
 /* Multi-GPU execution: one process per GPU, every process launches ONE kernel per solve.

@@ -11,13 +11,14 @@ import torch
 
 from ..ops import _native as N
 from ..ops import oracle, plan
-from ..ops.score import GpuExecutor
+from ..ops.score import GpuExecutor, NativeSession
 
 
 class AlignmentSolver:
     def __init__(self, device: str | torch.device | int = "cuda:0"):
         self.exec = GpuExecutor(device)
         self.device = self.exec.device
+        self.session = NativeSession(self.device.index or 0)
         self._pin_in = None
         self._pin_out = None
 
@@ -51,13 +52,17 @@ class AlignmentSolver:
         return host[:nseq, :3].numpy()
 
     def solve(self, problem) -> np.ndarray:
+        """The user-facing call: one native session solve (pack, H2D, kernel, D2H, sync)."""
         try:
-            blob = self.pack(problem)
+            return self.session.solve(problem)
         except N.NativeError as e:
             if e.code == N.SA_ERR_UNSUPPORTED:  # outside the GPU executor's limits
                 return oracle.solve_cpu(problem, "fast")
             raise
-        return self.solve_packed(blob).copy()
+
+    def solve_via_torch(self, problem) -> np.ndarray:
+        """Same result through torch-owned buffers on the current torch stream (pack() + solve_packed())."""
+        return self.solve_packed(self.pack(problem)).copy()
 
 
 _default: dict[str, AlignmentSolver] = {}

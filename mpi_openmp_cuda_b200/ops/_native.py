@@ -108,6 +108,14 @@ def cuda() -> C.CDLL:
     lib.sa_cuda_solve_problem.argtypes = [vp, C.POINTER(C.c_int32), C.c_int]
     lib.sa_cuda_solve_blob_noalloc.argtypes = [vp, C.POINTER(BlobHeader), vp, vp]
     lib.sa_cuda_launch_count.restype = C.c_uint64
+    lib.sa_session_create.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.sa_session_destroy.argtypes = [vp]
+    lib.sa_session_destroy.restype = None
+    lib.sa_session_solve.argtypes = [vp, vp, C.POINTER(C.c_int32)]
+    lib.sa_session_configure.argtypes = [vp, C.c_size_t, C.c_int]
+    lib.sa_session_configure.restype = None
+    lib.sa_session_last_bytes.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    lib.sa_session_last_bytes.restype = None
     return lib
 
 

@@ -73,3 +73,40 @@ class GpuExecutor:
     def solve_blob(self, blob: PackedBlob) -> torch.Tensor:
         self.upload(blob)
         return self.run(blob.header)
+
+
+class NativeSession:
+    """`sa_session`: the whole per-solve host path (plan + pack into pinned memory, H2D, launch,
+    D2H, synchronise) in ONE native call on a private stream — no Python between the steps."""
+
+    def __init__(self, device_index: int = 0):
+        self.lib = N.cuda()
+        self._h = C.c_void_p()
+        N.check(self.lib.sa_session_create(int(device_index), C.byref(self._h)))
+
+    def solve(self, problem):
+        import numpy as np
+
+        n = problem.nseq
+        out = np.empty((max(n, 1), 3), dtype=np.int32)
+        N.check(self.lib.sa_session_solve(self._h, problem.handle, out.ctypes.data_as(C.POINTER(C.c_int32))))
+        return out[:n]
+
+    def configure(self, zero_copy_max_bytes: int = 0, direct_out: bool = True) -> None:
+        self.lib.sa_session_configure(self._h, int(zero_copy_max_bytes), 1 if direct_out else 0)
+
+    def last_bytes(self) -> tuple[int, int]:
+        a, b = C.c_uint64(), C.c_uint64()
+        self.lib.sa_session_last_bytes(self._h, C.byref(a), C.byref(b))
+        return int(a.value), int(b.value)
+
+    def close(self):
+        if self._h is not None and self._h.value:
+            self.lib.sa_session_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

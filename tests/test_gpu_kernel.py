@@ -102,6 +102,14 @@ def test_c_abi_convenience_entry(shipped_inputs):
     assert np.array_equal(out, solve_cpu(p, "fast"))
 
 
+def test_native_session_and_torch_buffer_paths_agree(solver, shipped_inputs):
+    for i in (1, 3, 4):
+        p = Problem.from_file(shipped_inputs[i][0])
+        assert np.array_equal(solver.solve(p), solver.solve_via_torch(p))
+    h2d, d2h = solver.session.last_bytes()
+    assert h2d > 0 and d2h == 16 * 30
+
+
 def test_cpu_walk_and_gpu_agree_on_blob(solver, shipped_inputs):
     p = Problem.from_file(shipped_inputs[3][0])
     blob = solver.pack(p)
