@@ -84,9 +84,11 @@ inline uint64_t pack_key(int32_t score, uint32_t n) {
 
 extern "C" {
 
-int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, size_t* blob_bytes) {
+// mode: SA_MODE_AUTO picks SA_MODE_PAIR for large single-GPU batches when its limits hold,
+// SA_MODE_TILE otherwise. Forcing SA_MODE_PAIR on an input outside its limits is an error.
+int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_t cap, size_t* blob_bytes) {
     using namespace sa;
-    if (!p || !blob_bytes || world < 1 || world > SA_MAX_WORLD) {
+    if (!p || !blob_bytes || world < 1 || world > SA_MAX_WORLD || mode < SA_MODE_AUTO || mode > SA_MODE_PAIR) {
         set_error("sa_plan_pack: bad argument");
         return SA_ERR_ARG;
     }
@@ -103,9 +105,7 @@ int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, siz
         set_error("more than five distinct non-letter bytes in the input");
         return SA_ERR_UNSUPPORTED;
     }
-    std::vector<SeqPlan> plans(nseq);
-    uint32_t max_rows = kU, max_window = 16;
-    uint64_t total_cells = 0, padded_cells = 0, nitems64 = 0;
+    uint32_t max_len2 = 0, nvalid = 0;
     for (uint32_t s = 0; s < nseq; ++s) {
         const size_t l2 = p->seq2[s].size();
         if (l2 > SA_GPU_MAX_SEQ2) {
@@ -117,13 +117,114 @@ int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, siz
             set_error("weights too large for the int32 GPU path");
             return SA_ERR_UNSUPPORTED;
         }
-        plans[s] = plan_sequence(len1, (uint32_t)l2);
-        max_rows = std::max(max_rows, plans[s].rows_padded());
-        if (plans[s].ntiles)
-            max_window = std::max(max_window, round_up(plans[s].rows_padded() + (kWarpDiag << plans[s].wd_log2), 16));
+        max_len2 = std::max<uint32_t>(max_len2, (uint32_t)l2);
+        if (l2 <= len1) ++nvalid;
+    }
+
+    // ---- pair mode (two sequences per 32-bit lane as u16x2, per-pair profile in shared memory)
+    const int64_t vals[5] = {0, p->weights[0], -(int64_t)p->weights[1], -(int64_t)p->weights[2], -(int64_t)p->weights[3]};
+    const int64_t wmin = *std::min_element(vals, vals + 5), wmax = *std::max_element(vals, vals + 5);
+    const int64_t wrange = wmax - wmin;
+    struct Pair {
+        uint32_t a, b;  // b == SA_NO_SEQ: unpaired
+        SeqPlan g;
+    };
+    std::vector<Pair> pairs;
+    bool pair_ok = world == 1 && wrange <= 32767 && nvalid > 0;
+    std::string pair_why = world != 1 ? "pair mode is single-GPU" : (wrange > 32767 ? "weight range exceeds 16 bits" : "no sequence has candidates");
+    uint32_t pair_cols_needed = 0;
+    if (pair_ok && (mode == SA_MODE_PAIR || (mode == SA_MODE_AUTO && nvalid >= SA_PAIR_MIN_SEQS))) {
+        std::vector<uint32_t> order;
+        for (uint32_t s = 0; s < nseq; ++s)
+            if (p->seq2[s].size() <= len1) order.push_back(s);
+        std::stable_sort(order.begin(), order.end(),
+                         [&](uint32_t x, uint32_t y) { return p->seq2[x].size() > p->seq2[y].size(); });
+        for (size_t i = 0; i < order.size(); i += 2) {
+            Pair pr;
+            pr.a = order[i];
+            pr.b = i + 1 < order.size() ? order[i + 1] : SA_NO_SEQ;
+            const uint32_t ma = (uint32_t)p->seq2[pr.a].size();
+            const uint32_t mb = pr.b == SA_NO_SEQ ? ma : (uint32_t)p->seq2[pr.b].size();
+            const uint32_t rows = std::max(ma, mb), dmax = len1 - std::min(ma, mb);
+            // geometry: as plan_sequence, with the row-chunk length also bounded by the u16 range
+            SeqPlan g;
+            g.len = rows;
+            g.ndiag = (int32_t)dmax;
+            const uint32_t d = dmax == 0 ? 1u : dmax;
+            uint64_t best_cost = ~0ull;
+            for (uint32_t l = 0; (1u << l) <= kWarps; ++l) {
+                const uint32_t wd = 1u << l, wr = kWarps / wd;
+                const uint32_t crow = round_up((rows + wr - 1) / wr, kU);
+                if ((int64_t)crow * wrange > 32767) continue;
+                const uint32_t tn = kWarpDiag * wd, ntiles = (d + tn - 1) / tn;
+                const uint64_t cost = (uint64_t)ntiles * tn * wr * crow;
+                if (cost < best_cost) {
+                    best_cost = cost;
+                    g.wd_log2 = l;
+                    g.crow = crow;
+                    g.ntiles = ntiles;
+                    g.item_cost = cost;  // whole pair
+                }
+            }
+            if (best_cost == ~0ull) {
+                pair_ok = false;
+                pair_why = "a row chunk would overflow 16 bits";
+                break;
+            }
+            pr.g = g;
+            pair_cols_needed = std::max(pair_cols_needed, g.ntiles * (kWarpDiag << g.wd_log2) + g.rows_padded());
+            pairs.push_back(pr);
+        }
+        if (pair_ok) {
+            uint32_t mr = kU;
+            for (const Pair& pr : pairs) mr = std::max(mr, pr.g.rows_padded());
+            const uint64_t smem = (uint64_t)mr * 128 + 2ull * round_up(mr, 16) +
+                                  round_up(std::max(len1 + SA_SEQ1_TAIL_PAD, pair_cols_needed + 16u), 16) + SA_PAIR_FIXED_SMEM;
+            if (smem > SA_PAIR_MAX_SMEM) {
+                pair_ok = false;
+                pair_why = "pair profile does not fit in shared memory";
+            }
+        }
+    } else if (pair_ok) {
+        pair_ok = false;
+        pair_why = "batch too small for pair mode";
+    }
+    if (mode == SA_MODE_PAIR && !pair_ok) {
+        set_error("pair mode not applicable: " + pair_why);
+        return SA_ERR_UNSUPPORTED;
+    }
+    const bool use_pairs = pair_ok && mode != SA_MODE_TILE;
+
+    // ---- per-sequence plans
+    std::vector<SeqPlan> plans(nseq);
+    uint32_t max_rows = kU, max_window = 16;
+    uint64_t total_cells = 0, padded_cells = 0, nitems64 = 0;
+    for (uint32_t s = 0; s < nseq; ++s) {
+        plans[s] = plan_sequence(len1, (uint32_t)p->seq2[s].size());
         total_cells += (uint64_t)sa_problem_candidates(p, (int32_t)s);
-        padded_cells += plans[s].item_cost * plans[s].ntiles;
-        nitems64 += plans[s].ntiles;
+    }
+    if (use_pairs) {
+        for (const Pair& pr : pairs) {
+            for (uint32_t s : {pr.a, pr.b}) {
+                if (s == SA_NO_SEQ) continue;
+                const int32_t nd = plans[s].ndiag;
+                const uint32_t len = plans[s].len;
+                plans[s] = pr.g;  // both members share the pair's geometry
+                plans[s].ndiag = nd;
+                plans[s].len = len;
+            }
+            max_rows = std::max(max_rows, pr.g.rows_padded());
+            padded_cells += 2 * pr.g.item_cost;
+        }
+        nitems64 = pairs.size();
+    } else {
+        for (uint32_t s = 0; s < nseq; ++s) {
+            max_rows = std::max(max_rows, plans[s].rows_padded());
+            if (plans[s].ntiles)
+                max_window = std::max(max_window, round_up(plans[s].rows_padded() + (kWarpDiag << plans[s].wd_log2), 16));
+            padded_cells += plans[s].item_cost * plans[s].ntiles;
+            nitems64 += plans[s].ntiles;
+        }
     }
     if (nitems64 > 0x7FFFFFFFull) {
         set_error("too many work items");
@@ -132,7 +233,8 @@ int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, siz
     const uint32_t nitems = (uint32_t)nitems64;
 
     // ---- layout
-    const uint32_t len1_padded = round_up(len1 + SA_SEQ1_TAIL_PAD, 16);
+    uint32_t len1_padded = round_up(len1 + SA_SEQ1_TAIL_PAD, 16);
+    if (use_pairs) len1_padded = std::max(len1_padded, round_up(pair_cols_needed + 16u, 16));
     uint64_t off = sizeof(sa_blob_header);
     const uint32_t off_lut = (uint32_t)off;
     off += sizeof(int32_t) * SA_ALPHABET * SA_ALPHABET;
@@ -159,36 +261,41 @@ int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, siz
     if (!dst) return SA_OK;
     if (cap < total) {
         set_error("sa_plan_pack_into: destination too small");
-        return SA_ERR_ARG;
+        return SA_ERR_SMALL_BUFFER;
     }
 
     // ---- partition: deal sequences (or tiles, when sequences are scarce) to ranks
-    std::vector<uint32_t> order(nseq);
-    std::iota(order.begin(), order.end(), 0u);
-    std::stable_sort(order.begin(), order.end(),
-                     [&](uint32_t a, uint32_t b) { return plans[a].item_cost > plans[b].item_cost; });
     struct RankItem {
         uint32_t seq, tile;
     };
     std::vector<std::vector<RankItem>> per_rank((size_t)world);
-    std::vector<uint64_t> load((size_t)world, 0);
     std::vector<uint8_t> home(nseq, 0);
-    const bool by_tile = world > 1 && nseq < 2u * (uint32_t)world;
-    auto lightest = [&]() { return (int)(std::min_element(load.begin(), load.end()) - load.begin()); };
-    for (uint32_t s : order) {
-        const SeqPlan& sp = plans[s];
-        if (sp.ntiles == 0) continue;
-        if (!by_tile) {
-            const int r = lightest();
-            home[s] = (uint8_t)r;
-            for (uint32_t t = 0; t < sp.ntiles; ++t) per_rank[(size_t)r].push_back({s, t});
-            load[(size_t)r] += sp.item_cost * sp.ntiles;
-        } else {
-            for (uint32_t t = 0; t < sp.ntiles; ++t) {
+    if (use_pairs) {
+        std::stable_sort(pairs.begin(), pairs.end(), [](const Pair& x, const Pair& y) { return x.g.item_cost > y.g.item_cost; });
+        for (const Pair& pr : pairs) per_rank[0].push_back({pr.a, pr.b});
+    } else {
+        std::vector<uint32_t> order(nseq);
+        std::iota(order.begin(), order.end(), 0u);
+        std::stable_sort(order.begin(), order.end(),
+                         [&](uint32_t a, uint32_t b) { return plans[a].item_cost > plans[b].item_cost; });
+        std::vector<uint64_t> load((size_t)world, 0);
+        const bool by_tile = world > 1 && nseq < 2u * (uint32_t)world;
+        auto lightest = [&]() { return (int)(std::min_element(load.begin(), load.end()) - load.begin()); };
+        for (uint32_t s : order) {
+            const SeqPlan& sp = plans[s];
+            if (sp.ntiles == 0) continue;
+            if (!by_tile) {
                 const int r = lightest();
-                if (t == 0) home[s] = (uint8_t)r;
-                per_rank[(size_t)r].push_back({s, t});
-                load[(size_t)r] += sp.item_cost;
+                home[s] = (uint8_t)r;
+                for (uint32_t t = 0; t < sp.ntiles; ++t) per_rank[(size_t)r].push_back({s, t});
+                load[(size_t)r] += sp.item_cost * sp.ntiles;
+            } else {
+                for (uint32_t t = 0; t < sp.ntiles; ++t) {
+                    const int r = lightest();
+                    if (t == 0) home[s] = (uint8_t)r;
+                    per_rank[(size_t)r].push_back({s, t});
+                    load[(size_t)r] += sp.item_cost;
+                }
             }
         }
     }
@@ -200,7 +307,7 @@ int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, siz
     h->magic = SA_BLOB_MAGIC;
     h->version = SA_BLOB_VERSION;
     h->total_bytes = (uint32_t)total;
-    h->flags = 0;
+    h->flags = use_pairs ? SA_FLAG_PAIR_MODE : 0u;
     std::memcpy(h->weights, p->weights, sizeof(h->weights));
     h->len1 = len1;
     h->len1_padded = len1_padded;
@@ -220,6 +327,8 @@ int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, siz
     h->total_cells = total_cells;
     h->padded_cells = padded_cells;
     h->world = (uint32_t)world;
+    h->value_min = (int32_t)wmin;
+    h->value_range = (uint32_t)wrange;
     build_lut(al, p->weights, reinterpret_cast<int32_t*>(base + off_lut));
     for (uint32_t j = 0; j < len1; ++j) base[off_seq1 + j] = (unsigned char)(al.code[(unsigned char)p->seq1[j]] * 4);
     sa_seq_desc* tab = reinterpret_cast<sa_seq_desc*>(base + off_seqtab);
@@ -243,6 +352,10 @@ int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, siz
     }
     for (int r = world; r <= SA_MAX_WORLD; ++r) h->rank_first_item[r] = w;
     return SA_OK;
+}
+
+int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, size_t* blob_bytes) {
+    return sa_plan_pack_mode(p, world, SA_MODE_AUTO, dst, cap, blob_bytes);
 }
 
 int sa_plan_pack(const sa_problem* p, int world, void** blob, size_t* blob_bytes) {
@@ -304,6 +417,103 @@ int open_blob(const void* blob, size_t blob_bytes, BlobView* v) {
 
 }  // namespace
 
+namespace {
+
+// PAIR mode walk: bit-exact emulation of the kernel's u16x2 arithmetic (plain 32-bit adds on
+// biased, non-negative halves; per-half unsigned max), with checks that no half ever carries or
+// borrows into its neighbour — the property the planner's limits are there to guarantee.
+int score_pair_cpu(const BlobView& b, uint32_t it, uint64_t* keys) {
+    using namespace sa;
+    const uint32_t ia = b.items[it].seq, ib = b.items[it].tile;
+    const sa_seq_desc& da = b.tab[ia];
+    const sa_seq_desc* db = ib == SA_NO_SEQ ? nullptr : &b.tab[ib];
+    const uint32_t wd = 1u << da.wd_log2, wr = kWarps / wd, crow = da.crow, rows = crow * wr;
+    const uint32_t tn = kWarpDiag * wd;
+    const int32_t wmin = b.h->value_min;
+    const uint32_t BIG = 32767u, BIG2 = BIG | (BIG << 16);
+    const unsigned char* sA = b.base + da.off;
+    std::vector<unsigned char> zeros(rows, 0);
+    const unsigned char* sB = db ? b.base + db->off : zeros.data();
+    std::vector<uint32_t> prof((size_t)rows * SA_ALPHABET);
+    for (uint32_t row = 0; row < rows; ++row)
+        for (uint32_t c = 0; c < SA_ALPHABET; ++c) {
+            const int64_t ea = (int64_t)b.lut[sA[row] * SA_ALPHABET + c] - wmin;
+            const int64_t eb = (int64_t)b.lut[sB[row] * SA_ALPHABET + c] - wmin;
+            if (ea < 0 || eb < 0 || ea > 65535 || eb > 65535) {
+                set_error("pair walk: biased value outside u16");
+                return SA_ERR_ARG;
+            }
+            prof[(size_t)row * SA_ALPHABET + c] = (uint32_t)ea | ((uint32_t)eb << 16);
+        }
+    std::vector<uint32_t> csum((size_t)kWarps * (kR + 1) * 32), cmax((size_t)kWarps * kR * 32);
+    uint64_t keyA = 0, keyB = 0;
+    for (uint32_t tile = 0; tile < da.ntiles; ++tile) {
+        const uint32_t n0 = tile * tn;
+        if ((uint64_t)n0 + rows + tn > b.h->len1_padded) {
+            set_error("pair walk: window outside padded Seq1");
+            return SA_ERR_ARG;
+        }
+        for (uint32_t w = 0; w < kWarps; ++w) {
+            const uint32_t g = w & (wd - 1), q = w >> da.wd_log2;
+            for (uint32_t lane = 0; lane < 32; ++lane) {
+                const uint32_t d0 = g * kWarpDiag + lane * kR;
+                uint32_t P[kR + 1], best[kR];
+                for (uint32_t r = 0; r <= kR; ++r) P[r] = 0;
+                for (uint32_t r = 0; r < kR; ++r) best[r] = 0;
+                for (uint32_t i = q * crow; i < (q + 1) * crow; ++i) {
+                    for (uint32_t r = 0; r <= kR; ++r) {
+                        const uint32_t v = prof[(size_t)i * SA_ALPHABET + (b.seq1[n0 + i + d0 + r] >> 2)];
+                        if ((P[r] & 0xFFFFu) + (v & 0xFFFFu) > BIG || (P[r] >> 16) + (v >> 16) > BIG) {
+                            set_error("pair walk: prefix overflows its 16-bit lane");
+                            return SA_ERR_ARG;
+                        }
+                        P[r] += v;
+                    }
+                    for (uint32_t r = 0; r < kR; ++r) {
+                        const uint32_t t = P[r] + BIG2 - P[r + 1];  // no borrow: every half of P <= BIG
+                        const uint32_t lo = std::max(best[r] & 0xFFFFu, t & 0xFFFFu);
+                        const uint32_t hi = std::max(best[r] >> 16, t >> 16);
+                        best[r] = lo | (hi << 16);
+                    }
+                }
+                for (uint32_t r = 0; r <= kR; ++r) csum[((size_t)w * (kR + 1) + r) * 32 + lane] = P[r];
+                for (uint32_t r = 0; r < kR; ++r) cmax[((size_t)w * kR + r) * 32 + lane] = best[r];
+            }
+        }
+        for (uint32_t d = 0; d < tn; ++d) {
+            const uint32_t g = d / kWarpDiag, lane = (d % kWarpDiag) / kR, r = d % kR;
+            for (int half = 0; half < 2; ++half) {
+                const sa_seq_desc* sd = half == 0 ? &da : db;
+                if (!sd) continue;
+                const int sh = half * 16;
+                int32_t A = 0, T0 = 0, T1 = 0, M = kNeg;
+                for (uint32_t q = 0; q < wr; ++q) {
+                    const uint32_t w = q * wd + g;
+                    const int32_t s0 = (int32_t)((csum[((size_t)w * (kR + 1) + r) * 32 + lane] >> sh) & 0xFFFFu) + (int32_t)crow * wmin;
+                    const int32_t s1 = (int32_t)((csum[((size_t)w * (kR + 1) + r + 1) * 32 + lane] >> sh) & 0xFFFFu) + (int32_t)crow * wmin;
+                    const int32_t mx = (int32_t)((cmax[((size_t)w * kR + r) * 32 + lane] >> sh) & 0xFFFFu) - (int32_t)BIG;
+                    M = std::max(M, A + mx);
+                    A += s0 - s1;
+                    T0 += s0;
+                    T1 += s1;
+                }
+                const uint32_t n = n0 + d;
+                uint64_t& key = half == 0 ? keyA : keyB;
+                if (sd->ndiag == 0) {
+                    if (n == 0) key = std::max(key, pack_key(T0, 0));
+                } else if (n < (uint32_t)sd->ndiag) {
+                    key = std::max(key, pack_key(T1 + M, n));
+                }
+            }
+        }
+    }
+    keys[ia] = std::max(keys[ia], keyA);
+    if (db) keys[ib] = std::max(keys[ib], keyB);
+    return SA_OK;
+}
+
+}  // namespace
+
 int sa_blob_score_items_cpu(const void* blob, size_t blob_bytes, uint32_t first_item, uint32_t last_item,
                             uint64_t* keys) {
     using namespace sa;
@@ -313,6 +523,13 @@ int sa_blob_score_items_cpu(const void* blob, size_t blob_bytes, uint32_t first_
     if (!keys || first_item > last_item || last_item > b.h->nitems) {
         set_error("sa_blob_score_items_cpu: bad item range");
         return SA_ERR_ARG;
+    }
+    if (b.h->flags & SA_FLAG_PAIR_MODE) {
+        for (uint32_t it = first_item; it < last_item; ++it) {
+            rc = score_pair_cpu(b, it, keys);
+            if (rc != SA_OK) return rc;
+        }
+        return SA_OK;
     }
     std::vector<int32_t> csum((size_t)kWarps * (kR + 1) * 32), cmax((size_t)kWarps * kR * 32);
     for (uint32_t it = first_item; it < last_item; ++it) {

@@ -142,6 +142,57 @@ __device__ __forceinline__ uint32_t byte_of(uint32_t lo, uint32_t hi, int k) {  
     return ((k < 4 ? lo : hi) >> (8 * (k & 3))) & 0xFFu;
 }
 
+// First k in [0, m) whose candidate (n fixed) reaches `bestv` — the reference's strict-'>' update
+// keeps the first maximum (cudaFunctions.cu:118,161). Whole CTA; `c1` = Seq1 codes (x4) at the
+// winning offset (shared or global), `s2` = the sequence's codes in shared memory.
+// scan[kWarps], tmp[kWarps] and *slot are shared scratch; *slot must hold 0x7FFFFFFF on entry.
+__device__ __forceinline__ int first_k_on_diagonal(const int* lut_i, const unsigned char* s2, const unsigned char* c1,
+                                                   uint32_t m, int bestv, int* scan, int* tmp, uint32_t* slot) {
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint32_t per = (m + kThreads - 1) / kThreads;
+    const uint32_t i0 = min(tid * per, m), i1 = min(i0 + per, m);
+    int da = 0, sb = 0;
+    for (uint32_t i = i0; i < i1; ++i) {
+        const int* lrow = lut_i + (uint32_t)s2[i] * SA_ALPHABET;
+        const int a = lrow[c1[i] >> 2], b = lrow[c1[i + 1] >> 2];
+        da += a - b;
+        sb += b;
+    }
+    // block-wide exclusive scan of da, block sums of da and sb
+    int inc = da, tsb = sb;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int x = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+        if (lane >= (uint32_t)o) inc += x;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tsb += __shfl_xor_sync(0xFFFFFFFFu, tsb, o);
+    if (lane == 31) scan[warp] = inc;
+    if (lane == 0) tmp[warp] = tsb;
+    __syncthreads();
+    int before = 0, tot_da = 0, T1 = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+        const int x = scan[w];
+        if ((uint32_t)w < warp) before += x;
+        tot_da += x;
+        T1 += tmp[w];
+    }
+    const int T0 = T1 + tot_da;
+    if (T0 == bestv) return 0;  // k = 0 is tried first and wins the tie
+    int S = before + inc - da;
+    for (uint32_t i = i0; i < i1; ++i) {
+        const int* lrow = lut_i + (uint32_t)s2[i] * SA_ALPHABET;
+        S += lrow[c1[i] >> 2] - lrow[c1[i + 1] >> 2];
+        if (i + 1 < m && T1 + S == bestv) {
+            atomicMin(slot, i + 1u);
+            break;
+        }
+    }
+    __syncthreads();
+    return (int)*slot;
+}
+
 // ------------------------------------------------------------------ the kernel
 
 // kFabric = false: one GPU owns everything (p.key/p.cnt/p.out/p.ctrl are local).
@@ -394,55 +445,8 @@ __device__ __forceinline__ void score_body(const KParams& p) {
             const unsigned long long fk = red[0];
             const int bestv = (int)((uint32_t)(fk >> 32) ^ 0x80000000u);
             const uint32_t nwin = 0xFFFFFFFFu - (uint32_t)(fk & 0xFFFFFFFFull);
-            int kres = 0;
-            if (sd.ndiag != 0) {
-                const int* lut_i = reinterpret_cast<const int*>(lut_b);
-                const uint32_t m = sd.len;
-                const uint32_t per = (m + kThreads - 1) / kThreads;
-                const uint32_t i0 = min(tid * per, m), i1 = min(i0 + per, m);
-                const unsigned char* c1 = seq1g + nwin;
-                int da = 0, sb = 0;
-                for (uint32_t i = i0; i < i1; ++i) {
-                    const int* lrow = lut_i + (uint32_t)s2[i] * SA_ALPHABET;
-                    const int a = lrow[c1[i] >> 2], b = lrow[c1[i + 1] >> 2];
-                    da += a - b;
-                    sb += b;
-                }
-                // block-wide exclusive scan of da, block sums of da and sb
-                int inc = da, tsb = sb;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int x = __shfl_up_sync(0xFFFFFFFFu, inc, o);
-                    if (lane >= (uint32_t)o) inc += x;
-                }
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) tsb += __shfl_xor_sync(0xFFFFFFFFu, tsb, o);
-                if (lane == 31) scan[warp] = inc;
-                if (lane == 0) csum[warp] = tsb;
-                __syncthreads();
-                int before = 0, tot_da = 0, T1 = 0;
-#pragma unroll
-                for (int w = 0; w < kWarps; ++w) {
-                    const int x = scan[w];
-                    if ((uint32_t)w < warp) before += x;
-                    tot_da += x;
-                    T1 += csum[w];
-                }
-                const int T0 = T1 + tot_da;
-                if (T0 != bestv) {  // otherwise k = 0 wins the tie (checked first, cudaFunctions.cu:118,161)
-                    int S = before + inc - da;
-                    for (uint32_t i = i0; i < i1; ++i) {
-                        const int* lrow = lut_i + (uint32_t)s2[i] * SA_ALPHABET;
-                        S += lrow[c1[i] >> 2] - lrow[c1[i + 1] >> 2];
-                        if (i + 1 < m && T1 + S == bestv) {
-                            atomicMin(&ctl[2], i + 1u);
-                            break;
-                        }
-                    }
-                    __syncthreads();
-                    kres = (int)ctl[2];
-                }
-            }
+            const int kres = sd.ndiag == 0 ? 0 : first_k_on_diagonal(reinterpret_cast<const int*>(lut_b), s2, seq1g + nwin,
+                                                                      sd.len, bestv, scan, csum, &ctl[2]);
             if (tid == 0) {
                 out[seq] = make_int4(bestv, (int)nwin, kres, 0);
                 *keyp = 0ull;  // leave the scratch zeroed for the next launch
@@ -485,6 +489,215 @@ __device__ __forceinline__ void score_body(const KParams& p) {
 __global__ void __launch_bounds__(kThreads, 2) sa_score_kernel(const KParams p) { score_body<false>(p); }
 __global__ void __launch_bounds__(kThreads, 2) sa_score_fabric_kernel(const KParams p) { score_body<true>(p); }
 
+// ------------------------------------------------------------------ PAIR mode kernel
+//
+// Throughput mode for large batches (SA_MODE_PAIR). One CTA owns two sequences of similar length
+// end to end:
+//   * their biased pair values are laid out as ONE profile in shared memory,
+//     prof[row][letter] = (valueA - vmin) | (valueB - vmin) << 16, so a single conflict-free LDS
+//     feeds both sequences and its address is `letter register + immediate` (no per-cell math);
+//   * prefixes and running maxima are u16x2: P += v is a plain IADD (halves never carry: the
+//     planner bounds chunk_rows * value_range by 32767), the neighbour difference is one IADD3
+//     `P[r] + BIG - P[r+1]` (never borrows) and the running maximum is one DPX VIMNMX.U16x2;
+//   * Seq1 stays resident in shared memory for the whole kernel; no atomics, no fences: the tile
+//     loop keeps the two best keys in registers and the CTA finishes both sequences itself.
+__global__ void __launch_bounds__(kThreads, 1) sa_score_pair_kernel(const KParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
+    const uint32_t seq1_bytes = (hdr->len1_padded + 15u) & ~15u;
+    unsigned char* const lut_b = smem;
+    unsigned char* const seq1s = lut_b + kLutBytes;
+    unsigned char* const sA = seq1s + seq1_bytes;
+    unsigned char* const sB = sA + p.s2_cap;
+    uint32_t* const prof = reinterpret_cast<uint32_t*>(sB + p.s2_cap);
+    uint32_t* const csum = prof + (size_t)p.s2_cap * SA_ALPHABET;
+    uint32_t* const cmax = csum + kSumWords;
+    unsigned long long* const red = reinterpret_cast<unsigned long long*>(cmax + kMaxWords);  // [2 * kWarps]
+    unsigned long long* const mbar = red + 2 * kWarps;
+    int* const scan = reinterpret_cast<int*>(mbar + 1);               // [kWarps]
+    int* const tmp = scan + kWarps;                                   // [kWarps]
+    uint32_t* const ctl = reinterpret_cast<uint32_t*>(tmp + kWarps);  // [0] item, [2] first k
+
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + hdr->off_seqtab);
+    const sa_item* const items = reinterpret_cast<const sa_item*>(p.blob + hdr->off_items);
+    const int* const lut_i = reinterpret_cast<const int*>(lut_b);
+    const int vmin = hdr->value_min;
+    constexpr uint32_t BIG = 32767u, BIG2 = BIG | (BIG << 16);
+    const uint32_t bar = smem_u32(mbar);
+    uint32_t parity = 0;
+
+    if (p.write_empty) {
+        for (uint32_t s = blockIdx.x * kThreads + tid; s < hdr->nseq; s += gridDim.x * kThreads)
+            if (seqtab[s].ntiles == 0) p.out[s] = make_int4(INT_MIN, 0, 0, 0);
+    }
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (tid == 0) {  // table + the whole of Seq1, once per CTA
+        mbar_expect_tx(bar, kLutBytes + seq1_bytes);
+        bulk_g2s(smem_u32(lut_b), p.blob + hdr->off_lut, kLutBytes, bar);
+        bulk_g2s(smem_u32(seq1s), p.blob + hdr->off_seq1, seq1_bytes, bar);
+    }
+    mbar_wait(bar, parity);
+    parity ^= 1u;
+
+    for (;;) {
+        if (tid == 0) ctl[0] = p.item_begin + atomicAdd(&p.ctrl[kCtlNext], 1u);
+        __syncthreads();  // also: the previous pair's shared state is no longer read
+        const uint32_t item = ctl[0];
+        if (item >= p.item_end) break;
+        const uint32_t ia = items[item].seq, ib = items[item].tile;
+        const sa_seq_desc da = seqtab[ia];
+        const bool has_b = ib != SA_NO_SEQ;
+        sa_seq_desc db = da;
+        if (has_b) db = seqtab[ib];
+        const uint32_t wd_log2 = da.wd_log2, wd = 1u << wd_log2, wr = (uint32_t)kWarps >> wd_log2;
+        const uint32_t crow = da.crow, rows = crow * wr, tn = (uint32_t)SA_DIAG_PER_WARP << wd_log2;
+        const uint32_t s2_bytes = (rows + 15u) & ~15u;
+
+        if (tid == 0) {
+            mbar_expect_tx(bar, has_b ? 2u * s2_bytes : s2_bytes);
+            bulk_g2s(smem_u32(sA), p.blob + da.off, s2_bytes, bar);
+            if (has_b) bulk_g2s(smem_u32(sB), p.blob + db.off, s2_bytes, bar);
+        }
+        if (!has_b)
+            for (uint32_t i = tid; i < s2_bytes; i += kThreads) sB[i] = 0;  // an all-padding partner
+        mbar_wait(bar, parity);
+        parity ^= 1u;
+        __syncthreads();
+
+        // ---- pair profile: one warp per row, lane = letter
+        for (uint32_t idx = tid; idx < rows * SA_ALPHABET; idx += kThreads) {
+            const uint32_t row = idx >> 5, c = idx & 31u;
+            const uint32_t ea = (uint32_t)(lut_i[(uint32_t)sA[row] * SA_ALPHABET + c] - vmin);
+            const uint32_t eb = (uint32_t)(lut_i[(uint32_t)sB[row] * SA_ALPHABET + c] - vmin);
+            prof[idx] = ea | (eb << 16);
+        }
+        __syncthreads();
+
+        unsigned long long keyA = 0ull, keyB = 0ull;
+        const uint32_t g = warp & (wd - 1u), q = warp >> wd_log2;
+        const uint32_t d0 = g * SA_DIAG_PER_WARP + lane * kR;
+        for (uint32_t tile = 0; tile < da.ntiles; ++tile) {
+            const uint32_t n0 = tile * tn;
+            // ---- scan: this warp = offset group g, row chunk q
+            {
+                const unsigned char* wp = seq1s + n0 + d0 + q * crow;
+                const unsigned char* pb = reinterpret_cast<const unsigned char*>(prof) + (size_t)q * crow * (SA_ALPHABET * 4u);
+                uint32_t P[kR + 1], best[kR];
+#pragma unroll
+                for (int r = 0; r <= kR; ++r) P[r] = 0u;
+#pragma unroll
+                for (int r = 0; r < kR; ++r) best[r] = 0u;
+                uint2 lw0 = *reinterpret_cast<const uint2*>(wp);
+                for (uint32_t row = 0; row < crow; row += kU) {
+                    const uint2 lw1 = *reinterpret_cast<const uint2*>(wp + row + kU);
+                    const unsigned char* A[2 * kU];
+#pragma unroll
+                    for (int k = 0; k < kU; ++k) {
+                        A[k] = pb + byte_of(lw0.x, lw0.y, k);
+                        A[kU + k] = pb + byte_of(lw1.x, lw1.y, k);
+                    }
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) {
+                        uint32_t v[kR + 1];
+#pragma unroll
+                        for (int r = 0; r <= kR; ++r)
+                            v[r] = *reinterpret_cast<const uint32_t*>(A[u + r] + u * (SA_ALPHABET * 4));
+#pragma unroll
+                        for (int r = 0; r <= kR; ++r) P[r] += v[r];
+#pragma unroll
+                        for (int r = 0; r < kR; ++r) best[r] = __vmaxu2(best[r], P[r] + BIG2 - P[r + 1]);
+                    }
+                    lw0 = lw1;
+                    pb += kU * (SA_ALPHABET * 4u);
+                }
+#pragma unroll
+                for (int r = 0; r <= kR; ++r) csum[(warp * (kR + 1) + r) * 32 + lane] = P[r];
+#pragma unroll
+                for (int r = 0; r < kR; ++r) cmax[(warp * kR + r) * 32 + lane] = best[r];
+            }
+            __syncthreads();
+            // ---- merge row chunks in order for both sequences, keep the best offsets so far
+            const int cbias = (int)crow * vmin;
+            for (uint32_t t = tid; t < tn; t += kThreads) {
+                const uint32_t l = t & 31u, r = (t >> 5) & 7u, gg = t >> 8;
+                int A0 = 0, T00 = 0, T10 = 0, M0 = kNeg, A1 = 0, T01 = 0, T11 = 0, M1 = kNeg;
+                for (uint32_t qq = 0; qq < wr; ++qq) {
+                    const uint32_t w = (qq << wd_log2) + gg;
+                    const uint32_t s0 = csum[(w * (kR + 1) + r) * 32 + l];
+                    const uint32_t s1 = csum[(w * (kR + 1) + r + 1) * 32 + l];
+                    const uint32_t mx = cmax[(w * kR + r) * 32 + l];
+                    const int s0a = (int)(s0 & 0xFFFFu) + cbias, s1a = (int)(s1 & 0xFFFFu) + cbias;
+                    const int s0b = (int)(s0 >> 16) + cbias, s1b = (int)(s1 >> 16) + cbias;
+                    M0 = max(M0, A0 + (int)(mx & 0xFFFFu) - (int)BIG);
+                    M1 = max(M1, A1 + (int)(mx >> 16) - (int)BIG);
+                    A0 += s0a - s1a;
+                    A1 += s0b - s1b;
+                    T00 += s0a;
+                    T10 += s1a;
+                    T01 += s0b;
+                    T11 += s1b;
+                }
+                const uint32_t n = n0 + gg * SA_DIAG_PER_WARP + l * kR + r;
+                if (da.ndiag == 0) {
+                    if (n == 0) keyA = pack_key(T00, 0u);
+                } else if (n < (uint32_t)da.ndiag) {
+                    keyA = umax64(keyA, pack_key(T10 + M0, n));
+                }
+                if (has_b) {
+                    if (db.ndiag == 0) {
+                        if (n == 0) keyB = pack_key(T01, 0u);
+                    } else if (n < (uint32_t)db.ndiag) {
+                        keyB = umax64(keyB, pack_key(T11 + M1, n));
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        // ---- block argmax for both sequences
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            keyA = umax64(keyA, __shfl_xor_sync(0xFFFFFFFFu, keyA, o));
+            keyB = umax64(keyB, __shfl_xor_sync(0xFFFFFFFFu, keyB, o));
+        }
+        if (lane == 0) {
+            red[warp] = keyA;
+            red[kWarps + warp] = keyB;
+        }
+        __syncthreads();
+        unsigned long long fa = 0ull, fb = 0ull;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) {
+            fa = umax64(fa, red[w]);
+            fb = umax64(fb, red[kWarps + w]);
+        }
+        // ---- first k of each winner, results out
+        for (int half = 0; half < (has_b ? 2 : 1); ++half) {
+            const sa_seq_desc& sd = half == 0 ? da : db;
+            const unsigned long long fk = half == 0 ? fa : fb;
+            const int bestv = (int)((uint32_t)(fk >> 32) ^ 0x80000000u);
+            const uint32_t nwin = 0xFFFFFFFFu - (uint32_t)(fk & 0xFFFFFFFFull);
+            if (tid == 0) ctl[2] = 0x7FFFFFFFu;
+            __syncthreads();
+            const int kres = sd.ndiag == 0 ? 0 : first_k_on_diagonal(lut_i, half == 0 ? sA : sB, seq1s + nwin, sd.len, bestv, scan, tmp, &ctl[2]);
+            if (tid == 0) p.out[half == 0 ? ia : ib] = make_int4(bestv, (int)nwin, kres, 0);
+            __syncthreads();
+        }
+    }
+    if (tid == 0) {
+        __threadfence();
+        const unsigned int done = atomicAdd(&p.ctrl[kCtlCtasDone], 1u);
+        if (done + 1u == gridDim.x) {
+            p.ctrl[kCtlNext] = 0u;
+            p.ctrl[kCtlCtasDone] = 0u;
+        }
+    }
+}
+
 // ------------------------------------------------------------------ host side
 
 std::atomic<uint64_t> g_launches{0};
@@ -495,6 +708,7 @@ struct DeviceInfo {
     int max_optin_smem = 0;
     int smem_set = 0;
     int smem_fabric_set = 0;
+    int smem_pair_set = 0;
 };
 std::mutex g_mu;
 DeviceInfo g_dev[64];
@@ -563,7 +777,7 @@ int sa_cuda_solve_blob(const void* d_blob, const sa_blob_header* h, int32_t* d_o
     int rc = device_info(dev, &di);
     if (rc != SA_OK) return rc;
 
-    KParams p;
+    KParams p{};
     p.blob = static_cast<const unsigned char*>(d_blob);
     p.out = reinterpret_cast<int4*>(d_out);
     unsigned char* sc = static_cast<unsigned char*>(d_scratch);
@@ -575,6 +789,28 @@ int sa_cuda_solve_blob(const void* d_blob, const sa_blob_header* h, int32_t* d_o
     p.s2_cap = (h->max_rows_padded + 15u) & ~15u;
     p.win_cap = (h->max_window_bytes + 15u) & ~15u;
     p.write_empty = 1;
+    if (h->flags & SA_FLAG_PAIR_MODE) {
+        const uint32_t smem = kLutBytes + ((h->len1_padded + 15u) & ~15u) + 2u * p.s2_cap + p.s2_cap * SA_ALPHABET * 4u +
+                              (kSumWords + kMaxWords) * 4u + 2u * kWarps * 8u + 8u + 2u * kWarps * 4u + 16u;
+        if ((int)smem > di->max_optin_smem) {
+            sa_set_last_error("sa_cuda_solve_blob: pair profile needs more shared memory than the device has");
+            return SA_ERR_UNSUPPORTED;
+        }
+        {
+            std::lock_guard<std::mutex> lock(g_mu);
+            if ((int)smem > di->smem_pair_set) {
+                SA_CUDA_TRY(cudaFuncSetAttribute(sa_score_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                di->smem_pair_set = (int)smem;
+            }
+        }
+        const uint32_t per_sm = smem + 1024u <= (uint32_t)di->max_optin_smem / 2u ? 2u : 1u;
+        uint32_t grid = (uint32_t)di->sm_count * per_sm;
+        if (h->nitems < grid) grid = h->nitems ? h->nitems : 1u;
+        sa_score_pair_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+        SA_CUDA_TRY(cudaGetLastError());
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        return SA_OK;
+    }
     const uint32_t smem = smem_bytes_for(p.s2_cap, p.win_cap);
     if ((int)smem > di->max_optin_smem) {
         sa_set_last_error("sa_cuda_solve_blob: problem needs more shared memory than the device has");

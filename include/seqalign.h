@@ -51,7 +51,8 @@ enum sa_status {
     SA_ERR_UNSUPPORTED = 3, /* input outside the GPU executor's limits */
     SA_ERR_CUDA = 4,        /* a CUDA runtime call failed (see sa_last_error) */
     SA_ERR_NOMEM = 5,
-    SA_ERR_TOO_LARGE = 6    /* exceeds a fixed-capacity entry point's maximum */
+    SA_ERR_TOO_LARGE = 6,   /* exceeds a fixed-capacity entry point's maximum */
+    SA_ERR_SMALL_BUFFER = 7 /* caller buffer too small; the needed size is returned */
 };
 
 /* Thread-local human-readable description of the last failure. */
@@ -123,6 +124,21 @@ size_t sa_format(const int32_t* results, int32_t nseq, char* buf, size_t cap);
 
 #define SA_MAX_WORLD 16
 
+/* Execution modes of a packed problem (sa_blob_header.flags bit 0).
+ *  TILE: item = (sequence, offset tile), int32 lanes, pair values looked up in a 32x32 table;
+ *        any input, any number of GPUs, best latency for small batches.
+ *  PAIR: item = two sequences of similar length scored together as u16x2 lanes of one 32-bit
+ *        register against a per-pair profile in shared memory; the CTA owns both sequences end
+ *        to end (no atomics). Throughput mode for large single-GPU batches. */
+#define SA_MODE_AUTO 0
+#define SA_MODE_TILE 1
+#define SA_MODE_PAIR 2
+#define SA_FLAG_PAIR_MODE 1u
+#define SA_NO_SEQ 0xFFFFFFFFu
+#define SA_PAIR_MIN_SEQS 1024u          /* AUTO switches to PAIR from this many scorable sequences */
+#define SA_PAIR_FIXED_SMEM (44u << 10)  /* table + merge arrays + bookkeeping */
+#define SA_PAIR_MAX_SMEM (227u << 10)
+
 typedef struct sa_blob_header {
     uint32_t magic, version, total_bytes, flags;
     int32_t weights[4];
@@ -141,7 +157,9 @@ typedef struct sa_blob_header {
     uint64_t padded_cells; /* cells the tiling actually evaluates              */
     uint32_t world;        /* number of GPUs the item list is partitioned for  */
     uint32_t rank_first_item[SA_MAX_WORLD + 1]; /* rank r owns items [r], [r+1]) */
-    uint32_t reserved[20];
+    int32_t value_min;     /* min over {0, w1, -w2, -w3, -w4}: bias of the u16 pair lanes */
+    uint32_t value_range;  /* max - min of the same set                               */
+    uint32_t reserved[18];
 } sa_blob_header; /* 256 bytes */
 
 typedef struct sa_seq_desc {
@@ -155,8 +173,8 @@ typedef struct sa_seq_desc {
 } sa_seq_desc; /* 16 bytes */
 
 typedef struct sa_item {
-    uint32_t seq;
-    uint32_t tile;
+    uint32_t seq;  /* TILE: sequence          PAIR: first sequence of the pair              */
+    uint32_t tile; /* TILE: offset tile index PAIR: second sequence, or SA_NO_SEQ            */
 } sa_item;
 
 /* Plan (choose per-sequence tiling, order items by cost) and pack everything
@@ -167,6 +185,8 @@ int sa_plan_pack(const sa_problem* p, int world, void** blob, size_t* blob_bytes
 /* Same, into caller memory (e.g. pinned): returns needed size in *blob_bytes
  * (call with dst == NULL to size the buffer). */
 int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, size_t* blob_bytes);
+/* As sa_plan_pack_into with an explicit SA_MODE_*. */
+int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_t cap, size_t* blob_bytes);
 void sa_blob_free(void* blob);
 
 /* CPU executor of a packed blob: walks the item list with exactly the tile /

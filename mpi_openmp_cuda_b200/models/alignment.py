@@ -33,10 +33,10 @@ class AlignmentSolver:
             self._pin_out = torch.empty((max(nseq, 64), 4), dtype=torch.int32, pin_memory=True)
         return self._pin_out
 
-    def pack(self, problem) -> plan.PackedBlob:
+    def pack(self, problem, mode: str = "auto") -> plan.PackedBlob:
         """Plan + pack straight into this solver's pinned staging buffer."""
-        need = plan.blob_size(problem, 1)
-        return plan.plan_pack(problem, 1, out=self._pinned_in(need))
+        need = plan.blob_size(problem, 1, mode)
+        return plan.plan_pack(problem, 1, out=self._pinned_in(need), mode=mode)
 
     def solve_packed(self, blob: plan.PackedBlob, sync: bool = True) -> np.ndarray:
         """H2D -> kernel -> D2H for an already packed problem. Returns int32[nseq,3]."""

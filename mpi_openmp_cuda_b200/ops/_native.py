@@ -14,6 +14,10 @@ from ..utils import build as _build
 SA_OK = 0
 SA_ERR_UNSUPPORTED = 3
 SA_ERR_TOO_LARGE = 6
+SA_ERR_SMALL_BUFFER = 7
+SA_MODE_AUTO, SA_MODE_TILE, SA_MODE_PAIR = 0, 1, 2
+SA_FLAG_PAIR_MODE = 1
+SA_NO_SEQ = 0xFFFFFFFF
 SA_MAX_WORLD = 16
 SA_NOALLOC_MAX_SEQ = 4096
 
@@ -28,7 +32,7 @@ class BlobHeader(C.Structure):
         ("max_rows_padded", C.c_uint32), ("max_window_bytes", C.c_uint32), ("chunk_bytes", C.c_uint32), ("nchunks", C.c_uint32), ("pad0", C.c_uint32),
         ("total_cells", C.c_uint64), ("padded_cells", C.c_uint64),
         ("world", C.c_uint32), ("rank_first_item", C.c_uint32 * (SA_MAX_WORLD + 1)),
-        ("reserved", C.c_uint32 * 20),
+        ("value_min", C.c_int32), ("value_range", C.c_uint32), ("reserved", C.c_uint32 * 18),
     ]
 
 
@@ -84,6 +88,7 @@ def core() -> C.CDLL:
     lib.sa_format.argtypes = [i32p, C.c_int32, C.c_void_p, sz]
     lib.sa_format.restype = sz
     lib.sa_plan_pack_into.argtypes = [vp, C.c_int, C.c_void_p, sz, C.POINTER(sz)]
+    lib.sa_plan_pack_mode.argtypes = [vp, C.c_int, C.c_int, C.c_void_p, sz, C.POINTER(sz)]
     lib.sa_blob_execute_cpu.argtypes = [C.c_void_p, sz, i32p]
     lib.sa_blob_score_items_cpu.argtypes = [C.c_void_p, sz, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
     lib.sa_blob_finalize_cpu.argtypes = [C.c_void_p, sz, C.POINTER(C.c_uint64), i32p]

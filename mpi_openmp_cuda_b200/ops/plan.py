@@ -27,6 +27,10 @@ class PackedBlob:
     def nitems(self) -> int:
         return int(self.header.nitems)
 
+    @property
+    def pair_mode(self) -> bool:
+        return bool(self.header.flags & N.SA_FLAG_PAIR_MODE)
+
     def numpy(self) -> np.ndarray:
         d = self.data
         return d if isinstance(d, np.ndarray) else d.numpy()
@@ -42,16 +46,20 @@ class PackedBlob:
         return raw.view(np.dtype([("seq", "<u4"), ("tile", "<u4")]))
 
 
-def blob_size(problem, world: int = 1) -> int:
+MODES = {"auto": N.SA_MODE_AUTO, "tile": N.SA_MODE_TILE, "pair": N.SA_MODE_PAIR}
+
+
+def blob_size(problem, world: int = 1, mode: str = "auto") -> int:
     need = C.c_size_t()
-    N.check(N.core().sa_plan_pack_into(problem.handle, world, None, 0, C.byref(need)))
+    N.check(N.core().sa_plan_pack_mode(problem.handle, world, MODES[mode], None, 0, C.byref(need)))
     return int(need.value)
 
 
-def plan_pack(problem, world: int = 1, pinned: bool = False, out=None) -> PackedBlob:
+def plan_pack(problem, world: int = 1, pinned: bool = False, out=None, mode: str = "auto") -> PackedBlob:
     """Plan the tiling, partition over `world` GPUs and pack. Raises NativeError with
-    code SA_ERR_UNSUPPORTED when the input is outside the GPU executor's limits."""
-    need = blob_size(problem, world)
+    code SA_ERR_UNSUPPORTED when the input is outside the GPU executor's limits.
+    mode: 'auto' | 'tile' (any input) | 'pair' (u16x2 throughput mode, single GPU)."""
+    need = blob_size(problem, world, mode)
     if out is not None:
         buf = out
         if buf.numel() < need:
@@ -66,7 +74,7 @@ def plan_pack(problem, world: int = 1, pinned: bool = False, out=None) -> Packed
         buf = np.empty(need, dtype=np.uint8)
         ptr = buf.ctypes.data
     got = C.c_size_t()
-    N.check(N.core().sa_plan_pack_into(problem.handle, world, C.c_void_p(ptr), need, C.byref(got)))
+    N.check(N.core().sa_plan_pack_mode(problem.handle, world, MODES[mode], C.c_void_p(ptr), need, C.byref(got)))
     hdr = N.BlobHeader.from_buffer_copy(C.string_at(ptr, C.sizeof(N.BlobHeader)))
     return PackedBlob(buf, int(got.value), hdr)
 

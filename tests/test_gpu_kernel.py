@@ -114,3 +114,52 @@ def test_cpu_walk_and_gpu_agree_on_blob(solver, shipped_inputs):
     p = Problem.from_file(shipped_inputs[3][0])
     blob = solver.pack(p)
     assert np.array_equal(solver.solve_packed(blob), plan.execute_blob_cpu(blob))
+
+
+# ---- PAIR mode (u16x2 lanes, per-pair profile): forced on small inputs, automatic on large batches
+
+@pytest.mark.parametrize("i", [1, 2, 3, 4, 5, 6])
+def test_pair_mode_golden_outputs(solver, shipped_inputs, i):
+    path, gold = shipped_inputs[i]
+    blob = solver.pack(Problem.from_file(path), mode="pair")
+    assert blob.pair_mode
+    assert format_results(solver.solve_packed(blob)) == gold.read_bytes()
+
+
+@pytest.mark.parametrize("seq1,seqs", EDGE)
+def test_pair_mode_edge_shapes(solver, seq1, seqs):
+    p = Problem.from_parts((5, 1, 2, 3), seq1, seqs)
+    assert np.array_equal(solver.solve_packed(solver.pack(p, mode="pair")), solve_cpu(p, "fast"))
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_pair_mode_random_vs_oracle(solver, seed):
+    rng = np.random.default_rng(300 + seed)
+    w = tuple(int(x) for x in rng.integers(0, 60, size=4))
+    len1 = int(rng.integers(30, 2500))
+    p = random_problem(61, len1=len1, len2_range=(1, min(len1 + 3, 1200)), weights=w, seed=seed)
+    blob = solver.pack(p, mode="pair")
+    assert np.array_equal(solver.solve_packed(blob), solve_cpu(p, "fast"))
+    assert np.array_equal(plan.execute_blob_cpu(blob), solve_cpu(p, "fast"))
+
+
+def test_auto_mode_picks_pairs_for_large_batches(solver):
+    p = random_problem(2500, len1=1400, len2_range=(40, 1100), seed=31)
+    blob = solver.pack(p)
+    assert blob.pair_mode
+    assert np.array_equal(solver.solve_packed(blob), solve_cpu(p, "fast"))
+    assert np.array_equal(solver.solve(p), solve_cpu(p, "fast"))  # native session, same auto choice
+    tile = solver.pack(p, mode="tile")
+    assert not tile.pair_mode
+    assert np.array_equal(solver.solve_packed(tile), solve_cpu(p, "fast"))
+
+
+def test_pair_mode_limits_fall_back_to_tiles(solver):
+    from mpi_openmp_cuda_b200.ops._native import NativeError
+
+    big_w = random_problem(1100, len1=300, len2_range=(20, 200), weights=(40000, 1, 1, 1), seed=5)
+    with pytest.raises(NativeError):
+        solver.pack(big_w, mode="pair")
+    blob = solver.pack(big_w)  # auto: weights do not fit 16 bits -> tiles
+    assert not blob.pair_mode
+    assert np.array_equal(solver.solve_packed(blob), solve_cpu(big_w, "fast"))
