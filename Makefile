@@ -6,7 +6,7 @@ NVCC      ?= $(CUDA_HOME)/bin/nvcc
 CXX       ?= g++
 PKG       := mpi_openmp_cuda_b200
 LIBDIR    := $(PKG)/_lib
-GENCODE   := -gencode arch=compute_100a,code=sm_100a
+GENCODE   := -gencode arch=compute_100a,code=[sm_100a,compute_100a]
 CXXFLAGS  := -O3 -std=c++17 -fPIC -Wall -Wextra -Iinclude -pthread
 NVCCFLAGS := -O3 -std=c++17 $(GENCODE) -lineinfo -Iinclude -Xcompiler -fPIC -Xptxas -v
 INPUT     ?= data/input1.txt

@@ -68,26 +68,42 @@ def main() -> int:
     a = ap.parse_args()
     if a.worker:
         return worker(a.cpu, a.timing_json)
-    port = _free_port()
-    procs = []
-    for r in range(a.gpus):
-        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(a.gpus), LOCAL_RANK=str(r),
-                   MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-        cmd = [sys.executable, "-m", "mpi_openmp_cuda_b200.parallel.launcher", "--worker", "--gpus", str(a.gpus)]
-        if a.cpu:
-            cmd.append("--cpu")
-        if a.timing_json:
-            cmd += ["--timing-json", a.timing_json]
-        procs.append(subprocess.Popen(cmd, env=env, stdin=None if r == 0 else subprocess.DEVNULL,
-                                      stdout=None if r == 0 else subprocess.DEVNULL))
-    rc = 0
-    for p in procs:
-        code = p.wait()
-        if code != 0 and rc == 0:
-            rc = code
-            for q in procs:  # a failed rank must not leave the others waiting
-                if q.poll() is None:
-                    q.kill()
+    data = sys.stdin.buffer.read()  # held by the parent so that a failed rendezvous can be retried
+    rc = 1
+    for attempt in range(3):
+        port = _free_port()
+        procs = []
+        for r in range(a.gpus):
+            env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(a.gpus), LOCAL_RANK=str(r),
+                       MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+            cmd = [sys.executable, "-m", "mpi_openmp_cuda_b200.parallel.launcher", "--worker", "--gpus", str(a.gpus)]
+            if a.cpu:
+                cmd.append("--cpu")
+            if a.timing_json:
+                cmd += ["--timing-json", a.timing_json]
+            procs.append(subprocess.Popen(cmd, env=env, stdin=subprocess.PIPE if r == 0 else subprocess.DEVNULL,
+                                          stdout=subprocess.PIPE if r == 0 else subprocess.DEVNULL,
+                                          stderr=subprocess.PIPE))
+        out0, err0 = procs[0].communicate(data)  # stdin goes to rank 0 only (main.c:68-108)
+        rc = procs[0].returncode
+        errs = [err0]
+        for q in procs[1:]:
+            if rc != 0 and q.poll() is None:
+                q.kill()  # a failed rank must not leave the others waiting
+            _, e = q.communicate()
+            errs.append(e)
+            if q.returncode != 0 and rc == 0:
+                rc = q.returncode
+        if rc == 0:
+            sys.stdout.buffer.write(out0)
+            sys.stdout.buffer.flush()
+            for e in errs:
+                sys.stderr.buffer.write(e)
+            return 0
+        if not any(b"EADDRINUSE" in e or b"address already in use" in e for e in errs):
+            break  # a real failure, not a rendezvous port collision
+    for e in errs:
+        sys.stderr.buffer.write(e)
     return rc
 
 
