@@ -23,7 +23,7 @@ for i in range(1, 7):
     text = path.read_bytes()
     p = Problem.parse(text)
     blob = solver.pack(p)
-    ok = format_results(solver.solve(p)) == gold
+    ok = format_results(solver.solve(p)) == gold and format_results(solver.solve_packed(blob)) == gold  # also uploads
     ks = []
     for _ in range(30):
         fl.flush()

@@ -218,6 +218,7 @@ __device__ __forceinline__ void score_body(const KParams& p) {
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
+    if (!kFabric && hdr->magic != SA_BLOB_MAGIC) return;  // never walk memory that is not a packed problem
     const uint32_t bar = smem_u32(mbar);
     uint32_t parity = 0;
     uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
@@ -504,6 +505,7 @@ __global__ void __launch_bounds__(kThreads, 2) sa_score_fabric_kernel(const KPar
 __global__ void __launch_bounds__(kThreads, 1) sa_score_pair_kernel(const KParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
+    if (hdr->magic != SA_BLOB_MAGIC) return;  // never walk memory that is not a packed problem
     const uint32_t seq1_bytes = (hdr->len1_padded + 15u) & ~15u;
     unsigned char* const lut_b = smem;
     unsigned char* const seq1s = lut_b + kLutBytes;
