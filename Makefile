@@ -13,7 +13,7 @@ INPUT     ?= data/input1.txt
 GPUS      ?= 1
 
 CORE_SRC := csrc/core/problem.cpp csrc/core/oracle.cpp csrc/core/plan.cpp
-CUDA_SRC := csrc/cuda/align_kernel.cu
+CUDA_SRC := csrc/cuda/align_kernel.cu csrc/cuda/fabric_bench.cu
 CORE_LIB := $(LIBDIR)/libseqalign_core.so
 CUDA_LIB := $(LIBDIR)/libseqalign_cuda.so
 

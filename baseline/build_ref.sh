@@ -26,6 +26,8 @@ echo "== step 2: MPI stand-in"
 cp "$HERE/mpi_shim/mpi.h" "$HERE/mpi_shim/shim_common.h" "$HERE/mpi_shim/mpicxx" "$OUT/shim/"
 g++ -O2 -fPIC -shared -o "$OUT/shim/libmpishim.so" "$HERE/mpi_shim/mpi_shim.cpp" -I"$HERE/mpi_shim" -lpthread || exit 1
 g++ -O2 -o "$OUT/bin/mpiexec" "$HERE/mpi_shim/mpiexec.cpp" -I"$HERE/mpi_shim" -lpthread || exit 1
+g++ -O2 -o "$OUT/bin/bench_coll" "$HERE/mpi_shim/bench_coll.cpp" -I"$HERE/mpi_shim" -L"$OUT/shim" -lmpishim -lpthread \
+    -Wl,-rpath,'$ORIGIN/../shim' || exit 1
 
 echo "== step 3: reference sources (verbatim)"
 if [ -d "$REF_SRC" ]; then

@@ -32,7 +32,9 @@ def parse_args():
     ap.add_argument("--scale", type=int, default=1,
                     help="replicate the input's sequences SCALE x per GPU (weak scaling: total = SCALE*gpus)")
     ap.add_argument("--synthetic", type=int, default=1024,
-                    help="also report the synthetic N-scaled config (x input3 per GPU; 0 = skip)")
+                    help="1 GPU: also report the synthetic N-scaled config (x input3; 0 = skip)")
+    ap.add_argument("--large", type=int, default=64,
+                    help="N > 1 GPUs: also report input3 x LARGE per GPU through the same fabric path (0 = skip)")
     return ap.parse_args()
 
 
@@ -135,7 +137,14 @@ def run_ours(args):
     if n_gpus > 1 or world > 1:
         from mpi_openmp_cuda_b200.parallel.dist_bench import time_ours_distributed
 
-        m = time_ours_distributed(problem, args.steps, args.warmup)
+        large_p = None
+        if args.large and rank == 0:
+            from mpi_openmp_cuda_b200.models.synthetic import scaled_input3
+
+            large_p = scaled_input3(args.large * n_gpus, ROOT / "data" / "input3.txt", seed=1)
+        elif args.large:
+            large_p = True  # other ranks only need to know that the phase exists
+        m = time_ours_distributed(problem, args.steps, args.warmup, large_p)
         if m is None:  # non-zero ranks print nothing
             return 0
     else:
@@ -182,6 +191,16 @@ def run_ours(args):
     }
     if args.synthetic and n_gpus == 1:
         line["synthetic"] = synthetic_report(args)
+    if m.get("fabric"):
+        line["fabric"] = m["fabric"]
+    if m.get("large"):
+        lg = m["large"]
+        if lg["nseq"] <= 4096:
+            assert np.array_equal(lg.pop("result"), solve_cpu(large_p, "fast")), "large config: GPU result differs from the CPU oracle"
+        lg.pop("result", None)
+        lg["config"] = f"input3 x{args.large} per GPU ({lg['nseq']} sequences), same fabric kernel"
+        lg["candidates_per_s"] = lg["candidates"] / (lg["kernel_ms"] * 1e-3)
+        line["large"] = lg
     print(json.dumps(line))
     return 0
 

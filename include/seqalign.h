@@ -314,6 +314,15 @@ typedef struct sa_fabric_desc {
  * peer_base[rank] + layout.off_ctrl + 12 if one of its waits timed out. */
 int sa_cuda_fabric_solve(const sa_fabric_desc* f, const sa_blob_header* header, void* stream);
 
+/* The two fabric primitives in isolation, for the 1 KB - 1 GB sweep against NCCL and the MPI path
+ * (BASELINE.json configs[4]). Both use the same symmetric buffer, flags and epoch discipline as
+ * sa_cuda_fabric_solve; every rank calls them once per operation.
+ *  bcast : rank 0's blob region [0, bytes) is replicated into every peer's blob region.
+ *  argmax: every rank's nkeys packed u64 keys are max-folded into rank 0's blob region (which rank 0
+ *          zeroes beforehand); rank 0's launch ends when all ranks have arrived. */
+int sa_cuda_fabric_bcast(const sa_fabric_desc* f, uint64_t bytes, int ctas, void* stream);
+int sa_cuda_fabric_argmax(const sa_fabric_desc* f, const void* d_keys, uint64_t nkeys, int ctas, void* stream);
+
 /* Number of kernel launches issued by this library in this process. */
 uint64_t sa_cuda_launch_count(void);
 

@@ -111,6 +111,24 @@ class Fabric:
         names = ["start", "prefix_ready", "items_done", "arrival_sent", "all_arrived"]
         return {n: (None if v in (0,) else (v - t[0]) / 1e3) for n, v in zip(names, t)} | {"start_abs_ns": t[0]}
 
+    # -- the two primitives in isolation (benchmarks/fabric_sweep.py)
+    def bcast(self, nbytes: int, ctas: int = 0) -> None:
+        """Replicate rank 0's blob region [0, nbytes) into every peer's blob region (collective)."""
+        self.lib.sa_cuda_fabric_bcast.argtypes = [C.POINTER(FabricDesc), C.c_uint64, C.c_int, C.c_void_p]
+        self.epoch += 1
+        self._desc.epoch = self.epoch
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        N.check(self.lib.sa_cuda_fabric_bcast(C.byref(self._desc), int(nbytes), int(ctas), C.c_void_p(stream)))
+
+    def argmax(self, keys: torch.Tensor, ctas: int = 0) -> None:
+        """Max-fold this rank's packed u64 keys (int64 tensor, non-negative) into rank 0's blob region."""
+        self.lib.sa_cuda_fabric_argmax.argtypes = [C.POINTER(FabricDesc), C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
+        self.epoch += 1
+        self._desc.epoch = self.epoch
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        N.check(self.lib.sa_cuda_fabric_argmax(C.byref(self._desc), C.c_void_p(keys.data_ptr()), int(keys.numel()),
+                                               int(ctas), C.c_void_p(stream)))
+
     def launch(self, header: N.BlobHeader | None) -> None:
         """Enqueue this rank's kernel of the next solve on the current stream."""
         self.epoch += 1
