@@ -36,8 +36,8 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ void multimem_st_v4(void* a, int4 v) {
     asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a), "r"(v.x), "r"(v.y), "r"(v.z),
@@ -70,9 +70,11 @@ __global__ void __launch_bounds__(kThreads) bcast_kernel(const BParams p) {
                 }
             }
             __syncthreads();
-            if (tid == 0)
+            if (tid == 0) {
+                __threadfence_system();  // one fence, then relaxed flag stores (not world-1 releases)
                 for (uint32_t r = 1; r < p.world; ++r)
-                    st_release_sys(reinterpret_cast<uint32_t*>(p.peer[r] + p.off_ctrl) + kCtlFlags + c, p.epoch);
+                    st_relaxed_sys(reinterpret_cast<uint32_t*>(p.peer[r] + p.off_ctrl) + kCtlFlags + c, p.epoch);
+            }
         }
     } else if (tid == 0) {
         const unsigned long long t0 = global_ns();
