@@ -17,7 +17,7 @@ from mpi_openmp_cuda_b200.utils.timing import L2Flusher  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--input", default="input3.txt")
 ap.add_argument("--scales", type=int, nargs="+", default=[1, 256, 1024])
-ap.add_argument("--modes", nargs="+", default=["tile", "pair"])
+ap.add_argument("--modes", nargs="+", default=["tile", "pair", "stream"])
 ap.add_argument("--iters", type=int, default=10)
 a = ap.parse_args()
 solver = AlignmentSolver("cuda:0")

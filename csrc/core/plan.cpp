@@ -48,7 +48,8 @@ struct SeqPlan {
     uint32_t wd_log2 = 0;
     uint32_t crow = kU;
     uint64_t item_cost = 0;  // padded cells per tile
-    uint32_t rows_padded() const { return crow * (kWarps >> wd_log2); }
+    bool stream = false;     // STREAM mode: one warp walks all rows (no row chunks)
+    uint32_t rows_padded() const { return stream ? crow : crow * (kWarps >> wd_log2); }
 };
 
 SeqPlan plan_sequence(uint32_t len1, uint32_t len2) {
@@ -92,7 +93,7 @@ extern "C" {
 // SA_MODE_TILE otherwise. Forcing SA_MODE_PAIR on an input outside its limits is an error.
 int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_t cap, size_t* blob_bytes) {
     using namespace sa;
-    if (!p || !blob_bytes || world < 1 || world > SA_MAX_WORLD || mode < SA_MODE_AUTO || mode > SA_MODE_PAIR) {
+    if (!p || !blob_bytes || world < 1 || world > SA_MAX_WORLD || mode < SA_MODE_AUTO || mode > SA_MODE_STREAM) {
         set_error("sa_plan_pack: bad argument");
         return SA_ERR_ARG;
     }
@@ -137,12 +138,25 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     bool pair_ok = world == 1 && wrange <= 32767 && nvalid > 0;
     std::string pair_why = world != 1 ? "pair mode is single-GPU" : (wrange > 32767 ? "weight range exceeds 16 bits" : "no sequence has candidates");
     uint32_t pair_cols_needed = 0;
-    if (pair_ok && (mode == SA_MODE_PAIR || (mode == SA_MODE_AUTO && nvalid >= SA_PAIR_MIN_SEQS))) {
+    const bool want_pairs = mode == SA_MODE_PAIR || mode == SA_MODE_STREAM || (mode == SA_MODE_AUTO && nvalid >= SA_PAIR_MIN_SEQS);
+    bool stream_ok = pair_ok && mode != SA_MODE_PAIR;
+    std::string stream_why = pair_why;
+    if (pair_ok && want_pairs) {
         std::vector<uint32_t> order;
         for (uint32_t s = 0; s < nseq; ++s)
             if (p->seq2[s].size() <= len1) order.push_back(s);
         std::stable_sort(order.begin(), order.end(),
                          [&](uint32_t x, uint32_t y) { return p->seq2[x].size() > p->seq2[y].size(); });
+        // STREAM needs every whole column of rows inside 16 bits
+        for (size_t i = 0; stream_ok && i < order.size(); i += 2)
+            if ((int64_t)round_up((uint32_t)p->seq2[order[i]].size(), SA_STREAM_ROW_BLOCK) * wrange > 32767) {
+                stream_ok = false;
+                stream_why = "a whole sequence would overflow 16 bits";
+            }
+        if (stream_ok && round_up(len1 + SA_SEQ1_TAIL_PAD, 16) > SA_STREAM_MAX_SEQ1) {
+            stream_ok = false;
+            stream_why = "Seq1 does not fit in shared memory next to the profile blocks";
+        }
         for (size_t i = 0; i < order.size(); i += 2) {
             Pair pr;
             pr.a = order[i];
@@ -150,11 +164,23 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
             const uint32_t ma = (uint32_t)p->seq2[pr.a].size();
             const uint32_t mb = pr.b == SA_NO_SEQ ? ma : (uint32_t)p->seq2[pr.b].size();
             const uint32_t rows = std::max(ma, mb), dmax = len1 - std::min(ma, mb);
-            // geometry: as plan_sequence, with the row-chunk length also bounded by the u16 range
             SeqPlan g;
             g.len = rows;
             g.ndiag = (int32_t)dmax;
             const uint32_t d = dmax == 0 ? 1u : dmax;
+            if (stream_ok) {
+                // one warp per (pair, 256-offset tile) walks every row in blocks of 32
+                g.stream = true;
+                g.wd_log2 = 0;
+                g.crow = round_up(rows, SA_STREAM_ROW_BLOCK);
+                g.ntiles = (d + kWarpDiag - 1) / kWarpDiag;
+                g.item_cost = (uint64_t)kWarpDiag * g.crow;  // per tile
+                pr.g = g;
+                pair_cols_needed = std::max(pair_cols_needed, g.ntiles * kWarpDiag + g.crow);
+                pairs.push_back(pr);
+                continue;
+            }
+            // PAIR geometry: as plan_sequence, with the row-chunk length also bounded by the u16 range
             uint64_t best_cost = ~0ull;
             for (uint32_t l = 0; (1u << l) <= kWarps; ++l) {
                 const uint32_t wd = 1u << l, wr = kWarps / wd;
@@ -179,7 +205,7 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
             pair_cols_needed = std::max(pair_cols_needed, g.ntiles * (kWarpDiag << g.wd_log2) + g.rows_padded());
             pairs.push_back(pr);
         }
-        if (pair_ok) {
+        if (pair_ok && !stream_ok) {
             uint32_t mr = kU;
             for (const Pair& pr : pairs) mr = std::max(mr, pr.g.rows_padded());
             const uint64_t smem = (uint64_t)mr * 128 + 2ull * round_up(mr, 16) +
@@ -191,13 +217,20 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
         }
     } else if (pair_ok) {
         pair_ok = false;
-        pair_why = "batch too small for pair mode";
+        stream_ok = false;
+        pair_why = stream_why = "batch too small for pair mode";
     }
+    if (!pair_ok) stream_ok = false;
     if (mode == SA_MODE_PAIR && !pair_ok) {
         set_error("pair mode not applicable: " + pair_why);
         return SA_ERR_UNSUPPORTED;
     }
+    if (mode == SA_MODE_STREAM && !stream_ok) {
+        set_error("stream mode not applicable: " + stream_why);
+        return SA_ERR_UNSUPPORTED;
+    }
     const bool use_pairs = pair_ok && mode != SA_MODE_TILE;
+    const bool use_stream = use_pairs && stream_ok;
 
     // ---- per-sequence plans
     std::vector<SeqPlan> plans(nseq);
@@ -218,9 +251,10 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
                 plans[s].len = len;
             }
             max_rows = std::max(max_rows, pr.g.rows_padded());
-            padded_cells += 2 * pr.g.item_cost;
+            padded_cells += 2 * pr.g.item_cost * (use_stream ? pr.g.ntiles : 1u);
+            if (use_stream) nitems64 += pr.g.ntiles;
         }
-        nitems64 = pairs.size();
+        if (!use_stream) nitems64 = pairs.size();
     } else {
         for (uint32_t s = 0; s < nseq; ++s) {
             max_rows = std::max(max_rows, plans[s].rows_padded());
@@ -250,6 +284,9 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     const uint32_t off_items = (uint32_t)off;
     off += (uint64_t)sizeof(sa_item) * nitems;
     off = (off + 15) / 16 * 16;
+    const uint32_t off_pairs = (uint32_t)off;
+    if (use_stream) off += (uint64_t)sizeof(sa_item) * pairs.size();
+    off = (off + 15) / 16 * 16;
     const uint32_t off_seq2 = (uint32_t)off;
     std::vector<uint32_t> seq_off(nseq);
     for (uint32_t s = 0; s < nseq; ++s) {
@@ -276,7 +313,12 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     std::vector<uint8_t> home(nseq, 0);
     if (use_pairs) {
         std::stable_sort(pairs.begin(), pairs.end(), [](const Pair& x, const Pair& y) { return x.g.item_cost > y.g.item_cost; });
-        for (const Pair& pr : pairs) per_rank[0].push_back({pr.a, pr.b});
+        if (use_stream) {
+            for (uint32_t pid = 0; pid < pairs.size(); ++pid)
+                for (uint32_t t = 0; t < pairs[pid].g.ntiles; ++t) per_rank[0].push_back({pid, t});
+        } else {
+            for (const Pair& pr : pairs) per_rank[0].push_back({pr.a, pr.b});
+        }
     } else {
         std::vector<uint32_t> order(nseq);
         std::iota(order.begin(), order.end(), 0u);
@@ -311,7 +353,13 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     h->magic = SA_BLOB_MAGIC;
     h->version = SA_BLOB_VERSION;
     h->total_bytes = (uint32_t)total;
-    h->flags = use_pairs ? SA_FLAG_PAIR_MODE : 0u;
+    h->flags = use_stream ? SA_FLAG_STREAM_MODE : (use_pairs ? SA_FLAG_PAIR_MODE : 0u);
+    h->off_pairs = use_stream ? off_pairs : 0u;
+    h->npairs = use_stream ? (uint32_t)pairs.size() : 0u;
+    if (use_stream) {
+        sa_item* pt = reinterpret_cast<sa_item*>(base + off_pairs);
+        for (uint32_t pid = 0; pid < pairs.size(); ++pid) pt[pid] = sa_item{pairs[pid].a, pairs[pid].b};
+    }
     std::memcpy(h->weights, p->weights, sizeof(h->weights));
     h->len1 = len1;
     h->len1_padded = len1_padded;
@@ -428,10 +476,17 @@ namespace {
 // borrows into its neighbour — the property the planner's limits are there to guarantee.
 int score_pair_cpu(const BlobView& b, uint32_t it, uint64_t* keys) {
     using namespace sa;
-    const uint32_t ia = b.items[it].seq, ib = b.items[it].tile;
+    // PAIR: the item is the pair, all its tiles, 16 warps = wd x wr.
+    // STREAM: the item is (pair, one tile), a single warp walks all rows (wd = wr = 1).
+    const bool stream = (b.h->flags & SA_FLAG_STREAM_MODE) != 0;
+    const sa_item* pairs = reinterpret_cast<const sa_item*>(b.base + b.h->off_pairs);
+    const uint32_t ia = stream ? pairs[b.items[it].seq].seq : b.items[it].seq;
+    const uint32_t ib = stream ? pairs[b.items[it].seq].tile : b.items[it].tile;
     const sa_seq_desc& da = b.tab[ia];
     const sa_seq_desc* db = ib == SA_NO_SEQ ? nullptr : &b.tab[ib];
-    const uint32_t wd = 1u << da.wd_log2, wr = kWarps / wd, crow = da.crow, rows = crow * wr;
+    const uint32_t nwarps = stream ? 1u : kWarps;
+    const uint32_t wd = 1u << da.wd_log2, wr = nwarps / wd, crow = da.crow, rows = crow * wr;
+    const uint32_t tile_begin = stream ? b.items[it].tile : 0u, tile_end = stream ? tile_begin + 1u : da.ntiles;
     const uint32_t tn = kWarpDiag * wd;
     const int32_t wmin = b.h->value_min;
     const uint32_t BIG = 32767u, BIG2 = BIG | (BIG << 16);
@@ -451,13 +506,13 @@ int score_pair_cpu(const BlobView& b, uint32_t it, uint64_t* keys) {
         }
     std::vector<uint32_t> csum((size_t)kWarps * (kR + 1) * 32), cmax((size_t)kWarps * kR * 32);
     uint64_t keyA = 0, keyB = 0;
-    for (uint32_t tile = 0; tile < da.ntiles; ++tile) {
+    for (uint32_t tile = tile_begin; tile < tile_end; ++tile) {
         const uint32_t n0 = tile * tn;
         if ((uint64_t)n0 + rows + tn > b.h->len1_padded) {
             set_error("pair walk: window outside padded Seq1");
             return SA_ERR_ARG;
         }
-        for (uint32_t w = 0; w < kWarps; ++w) {
+        for (uint32_t w = 0; w < nwarps; ++w) {
             const uint32_t g = w & (wd - 1), q = w >> da.wd_log2;
             for (uint32_t lane = 0; lane < 32; ++lane) {
                 const uint32_t d0 = g * kWarpDiag + lane * kR;
@@ -528,7 +583,7 @@ int sa_blob_score_items_cpu(const void* blob, size_t blob_bytes, uint32_t first_
         set_error("sa_blob_score_items_cpu: bad item range");
         return SA_ERR_ARG;
     }
-    if (b.h->flags & SA_FLAG_PAIR_MODE) {
+    if (b.h->flags & (SA_FLAG_PAIR_MODE | SA_FLAG_STREAM_MODE)) {
         for (uint32_t it = first_item; it < last_item; ++it) {
             rc = score_pair_cpu(b, it, keys);
             if (rc != SA_OK) return rc;

@@ -703,6 +703,222 @@ __global__ void __launch_bounds__(kThreads, 1) sa_score_pair_kernel(const KParam
     }
 }
 
+// ------------------------------------------------------------------ STREAM mode kernel
+//
+// SA_MODE_STREAM: the u16x2 arithmetic of PAIR mode without any block-level phase. Every WARP is
+// autonomous: it takes a (pair, 256-offset tile) from the queue and walks ALL rows of the pair,
+// 32 at a time; for each block of 32 rows it rebuilds a private 4 KB profile block
+// (lane = Seq1 letter, one conflict-free row per Seq2 position) and scans it with the same
+// LDS + IADD + IADD3 + VIMNMX.U16x2 inner loop. There is no row-chunk merge and no
+// __syncthreads after start-up; per-sequence keys are combined with atomics and the warp that
+// delivers a pair's last tile finishes both sequences on its own.
+__device__ __forceinline__ int warp_first_k(const uint32_t* lutlo, const unsigned char* g2, const unsigned char* c1,
+                                            uint32_t m, int bestv, int vmin, uint32_t lane) {
+    const uint32_t per = (m + 31u) >> 5;
+    const uint32_t i0 = min(lane * per, m), i1 = min(i0 + per, m);
+    int da = 0, sb = 0;
+    for (uint32_t i = i0; i < i1; ++i) {
+        const uint32_t* lrow = lutlo + (uint32_t)g2[i] * SA_ALPHABET;
+        const int a = (int)lrow[c1[i] >> 2], b = (int)lrow[c1[i + 1] >> 2];  // both biased: the bias cancels in a - b
+        da += a - b;
+        sb += b;
+    }
+    int inc = da, tsb = sb;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int x = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+        if (lane >= (uint32_t)o) inc += x;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tsb += __shfl_xor_sync(0xFFFFFFFFu, tsb, o);
+    const int T1 = tsb + (int)m * vmin;
+    const int T0 = T1 + __shfl_sync(0xFFFFFFFFu, inc, 31);
+    if (T0 == bestv) return 0;  // k = 0 is tried first and wins the tie
+    int S = inc - da;
+    uint32_t mine = 0x7FFFFFFFu;
+    for (uint32_t i = i0; i < i1; ++i) {
+        const uint32_t* lrow = lutlo + (uint32_t)g2[i] * SA_ALPHABET;
+        S += (int)lrow[c1[i] >> 2] - (int)lrow[c1[i + 1] >> 2];
+        if (i + 1 < m && T1 + S == bestv) {
+            mine = i + 1u;
+            break;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mine = min(mine, __shfl_xor_sync(0xFFFFFFFFu, mine, o));
+    return (int)mine;
+}
+
+__global__ void __launch_bounds__(kThreads, 2) sa_score_stream_kernel(const KParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
+    if (hdr->magic != SA_BLOB_MAGIC) return;  // never walk memory that is not a packed problem
+    const uint32_t seq1_bytes = (hdr->len1_padded + 15u) & ~15u;
+    uint32_t* const lutlo = reinterpret_cast<uint32_t*>(smem);
+    uint32_t* const luthi = lutlo + SA_ALPHABET * SA_ALPHABET;
+    unsigned char* const seq1s = reinterpret_cast<unsigned char*>(luthi + SA_ALPHABET * SA_ALPHABET);
+    uint32_t* const prof = reinterpret_cast<uint32_t*>(seq1s + seq1_bytes);
+    unsigned long long* const mbar = reinterpret_cast<unsigned long long*>(prof + kWarps * SA_STREAM_ROW_BLOCK * SA_ALPHABET);
+
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + hdr->off_seqtab);
+    const sa_item* const items = reinterpret_cast<const sa_item*>(p.blob + hdr->off_items);
+    const sa_item* const pairs = reinterpret_cast<const sa_item*>(p.blob + hdr->off_pairs);
+    const int vmin = hdr->value_min;
+    constexpr uint32_t BIG = 32767u, BIG2 = BIG | (BIG << 16);
+    const uint32_t bar = smem_u32(mbar);
+
+    if (p.write_empty) {
+        for (uint32_t s = blockIdx.x * kThreads + tid; s < hdr->nseq; s += gridDim.x * kThreads)
+            if (seqtab[s].ntiles == 0) p.out[s] = make_int4(INT_MIN, 0, 0, 0);
+    }
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (tid == 0) {  // raw table + the whole of Seq1, once per CTA
+        mbar_expect_tx(bar, kLutBytes + seq1_bytes);
+        bulk_g2s(smem_u32(lutlo), p.blob + hdr->off_lut, kLutBytes, bar);
+        bulk_g2s(smem_u32(seq1s), p.blob + hdr->off_seq1, seq1_bytes, bar);
+    }
+    mbar_wait(bar, 0u);
+    // biased table twice: low half for the first sequence of a pair, high half for the second
+    for (uint32_t i = tid; i < SA_ALPHABET * SA_ALPHABET; i += kThreads) {
+        const uint32_t v = (uint32_t)(reinterpret_cast<const int*>(lutlo)[i] - vmin);
+        lutlo[i] = v;
+        luthi[i] = v << 16;
+    }
+    __syncthreads();  // the last block-wide barrier of this kernel
+
+    uint32_t* const pw = prof + warp * (SA_STREAM_ROW_BLOCK * SA_ALPHABET);
+    const uint32_t d0 = lane * kR;
+    for (;;) {
+        uint32_t item = 0;
+        if (lane == 0) item = p.item_begin + atomicAdd(&p.ctrl[kCtlNext], 1u);
+        item = __shfl_sync(0xFFFFFFFFu, item, 0);
+        if (item >= p.item_end) break;
+        const uint32_t pid = items[item].seq, tile = items[item].tile;
+        const uint32_t ia = pairs[pid].seq, ib = pairs[pid].tile;
+        const bool has_b = ib != SA_NO_SEQ;
+        const sa_seq_desc da = seqtab[ia];
+        sa_seq_desc db = da;
+        if (has_b) db = seqtab[ib];
+        const uint32_t rows = da.crow, n0 = tile * SA_DIAG_PER_WARP;
+        const unsigned char* const gA = p.blob + da.off;
+        const unsigned char* const gB = p.blob + db.off;
+
+        uint32_t P[kR + 1], best[kR];
+#pragma unroll
+        for (int r = 0; r <= kR; ++r) P[r] = 0u;
+#pragma unroll
+        for (int r = 0; r < kR; ++r) best[r] = 0u;
+        const unsigned char* wp = seq1s + n0 + d0;
+        uint2 lw0 = *reinterpret_cast<const uint2*>(wp);
+        for (uint32_t rb = 0; rb < rows; rb += SA_STREAM_ROW_BLOCK) {
+            // ---- private profile block: row u, lane = letter
+            const uint32_t ca = (uint32_t)gA[rb + lane] * SA_ALPHABET + lane;
+            const uint32_t cb = has_b ? (uint32_t)gB[rb + lane] * SA_ALPHABET + lane : lane;
+#pragma unroll 8
+            for (uint32_t u = 0; u < SA_STREAM_ROW_BLOCK; ++u) {
+                const uint32_t a = __shfl_sync(0xFFFFFFFFu, ca, u) - u + lane;  // code*32 + my letter
+                const uint32_t b = __shfl_sync(0xFFFFFFFFu, cb, u) - u + lane;
+                pw[u * SA_ALPHABET + lane] = lutlo[a] | luthi[b];
+            }
+            __syncwarp();
+            // ---- scan the block: 4 trips of 8 rows
+            const unsigned char* pb = reinterpret_cast<const unsigned char*>(pw);
+#pragma unroll 1
+            for (uint32_t row = 0; row < SA_STREAM_ROW_BLOCK; row += kU) {
+                const uint2 lw1 = *reinterpret_cast<const uint2*>(wp + rb + row + kU);
+                const unsigned char* A[2 * kU];
+#pragma unroll
+                for (int k = 0; k < kU; ++k) {
+                    A[k] = pb + byte_of(lw0.x, lw0.y, k);
+                    A[kU + k] = pb + byte_of(lw1.x, lw1.y, k);
+                }
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    uint32_t v[kR + 1];
+#pragma unroll
+                    for (int r = 0; r <= kR; ++r) v[r] = *reinterpret_cast<const uint32_t*>(A[u + r] + u * (SA_ALPHABET * 4));
+#pragma unroll
+                    for (int r = 0; r <= kR; ++r) P[r] += v[r];
+#pragma unroll
+                    for (int r = 0; r < kR; ++r) best[r] = __vmaxu2(best[r], P[r] + BIG2 - P[r + 1]);
+                }
+                lw0 = lw1;
+                pb += kU * (SA_ALPHABET * 4u);
+            }
+            __syncwarp();
+        }
+        // ---- scores of this warp's 256 offsets for both sequences
+        const int vb = (int)rows * vmin;
+        unsigned long long keyA = 0ull, keyB = 0ull;
+#pragma unroll
+        for (int r = 0; r < kR; ++r) {
+            const uint32_t n = n0 + d0 + r;
+            const int t0a = (int)(P[r] & 0xFFFFu) + vb, t1a = (int)(P[r + 1] & 0xFFFFu) + vb;
+            const int t0b = (int)(P[r] >> 16) + vb, t1b = (int)(P[r + 1] >> 16) + vb;
+            const int ma = (int)(best[r] & 0xFFFFu) - (int)BIG, mb = (int)(best[r] >> 16) - (int)BIG;
+            if (da.ndiag == 0) {
+                if (n == 0) keyA = pack_key(t0a, 0u);
+            } else if (n < (uint32_t)da.ndiag) {
+                keyA = umax64(keyA, pack_key(t1a + ma, n));
+            }
+            if (has_b) {
+                if (db.ndiag == 0) {
+                    if (n == 0) keyB = pack_key(t0b, 0u);
+                } else if (n < (uint32_t)db.ndiag) {
+                    keyB = umax64(keyB, pack_key(t1b + mb, n));
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            keyA = umax64(keyA, __shfl_xor_sync(0xFFFFFFFFu, keyA, o));
+            keyB = umax64(keyB, __shfl_xor_sync(0xFFFFFFFFu, keyB, o));
+        }
+        uint32_t last = 0;
+        if (lane == 0) {
+            atomicMax(&p.key[ia], keyA);
+            if (has_b) atomicMax(&p.key[ib], keyB);
+            __threadfence();
+            last = (atomicAdd(&p.cnt[pid], 1u) + 1u == da.ntiles) ? 1u : 0u;
+        }
+        last = __shfl_sync(0xFFFFFFFFu, last, 0);
+        if (last) {  // this warp delivered the pair's last tile: finish both sequences
+            for (int half = 0; half < (has_b ? 2 : 1); ++half) {
+                const sa_seq_desc& sd = half == 0 ? da : db;
+                const uint32_t sidx = half == 0 ? ia : ib;
+                unsigned long long fk = 0ull;
+                if (lane == 0) {
+                    __threadfence();
+                    fk = atomicMax(&p.key[sidx], 0ull);
+                }
+                fk = __shfl_sync(0xFFFFFFFFu, fk, 0);
+                const int bestv = (int)((uint32_t)(fk >> 32) ^ 0x80000000u);
+                const uint32_t nwin = 0xFFFFFFFFu - (uint32_t)(fk & 0xFFFFFFFFull);
+                const int kres = sd.ndiag == 0 ? 0 : warp_first_k(lutlo, half == 0 ? gA : gB, seq1s + nwin, sd.len, bestv, vmin, lane);
+                if (lane == 0) {
+                    p.out[sidx] = make_int4(bestv, (int)nwin, kres, 0);
+                    p.key[sidx] = 0ull;
+                }
+            }
+            if (lane == 0) p.cnt[pid] = 0u;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        const unsigned int done = atomicAdd(&p.ctrl[kCtlCtasDone], 1u);
+        if (done + 1u == gridDim.x) {
+            p.ctrl[kCtlNext] = 0u;
+            p.ctrl[kCtlCtasDone] = 0u;
+        }
+    }
+}
+
 // ------------------------------------------------------------------ host side
 
 std::atomic<uint64_t> g_launches{0};
@@ -714,6 +930,7 @@ struct DeviceInfo {
     int smem_set = 0;
     int smem_fabric_set = 0;
     int smem_pair_set = 0;
+    int smem_stream_set = 0;
 };
 std::mutex g_mu;
 DeviceInfo g_dev[64];
@@ -794,6 +1011,28 @@ int sa_cuda_solve_blob(const void* d_blob, const sa_blob_header* h, int32_t* d_o
     p.s2_cap = (h->max_rows_padded + 15u) & ~15u;
     p.win_cap = (h->max_window_bytes + 15u) & ~15u;
     p.write_empty = 1;
+    if (h->flags & SA_FLAG_STREAM_MODE) {
+        const uint32_t smem = 2u * kLutBytes + ((h->len1_padded + 15u) & ~15u) +
+                              (uint32_t)kWarps * SA_STREAM_ROW_BLOCK * SA_ALPHABET * 4u + 64u;
+        if ((int)smem > di->max_optin_smem) {
+            sa_set_last_error("sa_cuda_solve_blob: Seq1 too long for the stream kernel's shared memory");
+            return SA_ERR_UNSUPPORTED;
+        }
+        {
+            std::lock_guard<std::mutex> lock(g_mu);
+            if ((int)smem > di->smem_stream_set) {
+                SA_CUDA_TRY(cudaFuncSetAttribute(sa_score_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                di->smem_stream_set = (int)smem;
+            }
+        }
+        uint32_t grid = (uint32_t)di->sm_count * 2u;
+        const uint32_t need = (h->nitems + kWarps - 1u) / kWarps;
+        if (need < grid) grid = need ? need : 1u;
+        sa_score_stream_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+        SA_CUDA_TRY(cudaGetLastError());
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        return SA_OK;
+    }
     if (h->flags & SA_FLAG_PAIR_MODE) {
         const uint32_t smem = kLutBytes + ((h->len1_padded + 15u) & ~15u) + 2u * p.s2_cap + p.s2_cap * SA_ALPHABET * 4u +
                               (kSumWords + kMaxWords) * 4u + 2u * kWarps * 8u + 8u + 2u * kWarps * 4u + 16u;

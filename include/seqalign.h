@@ -129,11 +129,19 @@ size_t sa_format(const int32_t* results, int32_t nseq, char* buf, size_t cap);
  *        any input, any number of GPUs, best latency for small batches.
  *  PAIR: item = two sequences of similar length scored together as u16x2 lanes of one 32-bit
  *        register against a per-pair profile in shared memory; the CTA owns both sequences end
- *        to end (no atomics). Throughput mode for large single-GPU batches. */
+ *        to end (no atomics). Throughput mode for large single-GPU batches.
+ *  STREAM: as PAIR (u16x2 lanes), but one WARP owns a (pair, 256-offset tile) and walks all rows,
+ *        rebuilding a private 32-row profile block as it goes: no block barriers, no row-chunk
+ *        merge; per-sequence keys are combined with atomics as in TILE. Preferred by AUTO when
+ *        rows * value_range fits 16 bits. */
 #define SA_MODE_AUTO 0
 #define SA_MODE_TILE 1
 #define SA_MODE_PAIR 2
+#define SA_MODE_STREAM 3
 #define SA_FLAG_PAIR_MODE 1u
+#define SA_FLAG_STREAM_MODE 2u
+#define SA_STREAM_ROW_BLOCK 32u
+#define SA_STREAM_MAX_SEQ1 (24u << 10)  /* padded Seq1 bytes that may stay resident in shared memory */
 #define SA_NO_SEQ 0xFFFFFFFFu
 #define SA_PAIR_MIN_SEQS 1024u          /* AUTO switches to PAIR from this many scorable sequences */
 #define SA_PAIR_FIXED_SMEM (44u << 10)  /* table + merge arrays + bookkeeping */
@@ -159,7 +167,9 @@ typedef struct sa_blob_header {
     uint32_t rank_first_item[SA_MAX_WORLD + 1]; /* rank r owns items [r], [r+1]) */
     int32_t value_min;     /* min over {0, w1, -w2, -w3, -w4}: bias of the u16 pair lanes */
     uint32_t value_range;  /* max - min of the same set                               */
-    uint32_t reserved[18];
+    uint32_t off_pairs;    /* STREAM: sa_item[npairs] = (first, second or SA_NO_SEQ)  */
+    uint32_t npairs;
+    uint32_t reserved[16];
 } sa_blob_header; /* 256 bytes */
 
 typedef struct sa_seq_desc {
@@ -173,8 +183,8 @@ typedef struct sa_seq_desc {
 } sa_seq_desc; /* 16 bytes */
 
 typedef struct sa_item {
-    uint32_t seq;  /* TILE: sequence          PAIR: first sequence of the pair              */
-    uint32_t tile; /* TILE: offset tile index PAIR: second sequence, or SA_NO_SEQ            */
+    uint32_t seq;  /* TILE: sequence          PAIR: first sequence     STREAM: pair index    */
+    uint32_t tile; /* TILE: offset tile index PAIR: second / SA_NO_SEQ STREAM: offset tile   */
 } sa_item;
 
 /* Plan (choose per-sequence tiling, order items by cost) and pack everything

@@ -15,8 +15,9 @@ SA_OK = 0
 SA_ERR_UNSUPPORTED = 3
 SA_ERR_TOO_LARGE = 6
 SA_ERR_SMALL_BUFFER = 7
-SA_MODE_AUTO, SA_MODE_TILE, SA_MODE_PAIR = 0, 1, 2
+SA_MODE_AUTO, SA_MODE_TILE, SA_MODE_PAIR, SA_MODE_STREAM = 0, 1, 2, 3
 SA_FLAG_PAIR_MODE = 1
+SA_FLAG_STREAM_MODE = 2
 SA_NO_SEQ = 0xFFFFFFFF
 SA_MAX_WORLD = 16
 SA_NOALLOC_MAX_SEQ = 4096
@@ -32,7 +33,7 @@ class BlobHeader(C.Structure):
         ("max_rows_padded", C.c_uint32), ("max_window_bytes", C.c_uint32), ("chunk_bytes", C.c_uint32), ("nchunks", C.c_uint32), ("pad0", C.c_uint32),
         ("total_cells", C.c_uint64), ("padded_cells", C.c_uint64),
         ("world", C.c_uint32), ("rank_first_item", C.c_uint32 * (SA_MAX_WORLD + 1)),
-        ("value_min", C.c_int32), ("value_range", C.c_uint32), ("reserved", C.c_uint32 * 18),
+        ("value_min", C.c_int32), ("value_range", C.c_uint32), ("off_pairs", C.c_uint32), ("npairs", C.c_uint32), ("reserved", C.c_uint32 * 16),
     ]
 
 

@@ -31,6 +31,14 @@ class PackedBlob:
     def pair_mode(self) -> bool:
         return bool(self.header.flags & N.SA_FLAG_PAIR_MODE)
 
+    @property
+    def stream_mode(self) -> bool:
+        return bool(self.header.flags & N.SA_FLAG_STREAM_MODE)
+
+    @property
+    def mode(self) -> str:
+        return "stream" if self.stream_mode else ("pair" if self.pair_mode else "tile")
+
     def numpy(self) -> np.ndarray:
         d = self.data
         return d if isinstance(d, np.ndarray) else d.numpy()
@@ -46,7 +54,7 @@ class PackedBlob:
         return raw.view(np.dtype([("seq", "<u4"), ("tile", "<u4")]))
 
 
-MODES = {"auto": N.SA_MODE_AUTO, "tile": N.SA_MODE_TILE, "pair": N.SA_MODE_PAIR}
+MODES = {"auto": N.SA_MODE_AUTO, "tile": N.SA_MODE_TILE, "pair": N.SA_MODE_PAIR, "stream": N.SA_MODE_STREAM}
 
 
 def blob_size(problem, world: int = 1, mode: str = "auto") -> int:

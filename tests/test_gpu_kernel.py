@@ -146,7 +146,11 @@ def test_pair_mode_random_vs_oracle(solver, seed):
 def test_auto_mode_picks_pairs_for_large_batches(solver):
     p = random_problem(2500, len1=1400, len2_range=(40, 1100), seed=31)
     blob = solver.pack(p)
-    assert blob.pair_mode
+    assert blob.mode == "stream"
+    pair = solver.pack(p, mode="pair")
+    assert pair.mode == "pair"
+    assert np.array_equal(solver.solve_packed(pair), solve_cpu(p, "fast"))
+    blob = solver.pack(p)
     assert np.array_equal(solver.solve_packed(blob), solve_cpu(p, "fast"))
     assert np.array_equal(solver.solve(p), solve_cpu(p, "fast"))  # native session, same auto choice
     tile = solver.pack(p, mode="tile")
@@ -163,3 +167,30 @@ def test_pair_mode_limits_fall_back_to_tiles(solver):
     blob = solver.pack(big_w)  # auto: weights do not fit 16 bits -> tiles
     assert not blob.pair_mode
     assert np.array_equal(solver.solve_packed(blob), solve_cpu(big_w, "fast"))
+
+
+# ---- STREAM mode (warp-autonomous u16x2, private profile blocks, no block barriers)
+
+@pytest.mark.parametrize("i", [1, 2, 3, 4, 5, 6])
+def test_stream_mode_golden_outputs(solver, shipped_inputs, i):
+    path, gold = shipped_inputs[i]
+    blob = solver.pack(Problem.from_file(path), mode="stream")
+    assert blob.stream_mode
+    for _ in range(2):  # twice: the scratch must come back zeroed
+        assert format_results(solver.solve_packed(blob)) == gold.read_bytes()
+
+
+@pytest.mark.parametrize("seq1,seqs", EDGE)
+def test_stream_mode_edge_shapes(solver, seq1, seqs):
+    p = Problem.from_parts((5, 1, 2, 3), seq1, seqs)
+    assert np.array_equal(solver.solve_packed(solver.pack(p, mode="stream")), solve_cpu(p, "fast"))
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_stream_mode_random_vs_oracle(solver, seed):
+    rng = np.random.default_rng(600 + seed)
+    w = tuple(int(x) for x in rng.integers(0, 14, size=4))
+    len1 = int(rng.integers(30, 2500))
+    p = random_problem(301, len1=len1, len2_range=(1, min(len1 + 3, 1200)), weights=w, seed=seed)
+    blob = solver.pack(p, mode="stream")
+    assert np.array_equal(solver.solve_packed(blob), solve_cpu(p, "fast"))

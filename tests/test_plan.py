@@ -143,9 +143,45 @@ def test_pair_mode_auto_threshold_and_limits():
     small = random_problem(50, len1=200, len2_range=(10, 100), seed=1)
     assert not plan.plan_pack(small).pair_mode                      # too few sequences
     assert not plan.plan_pack(random_problem(1200, len1=200, len2_range=(10, 100), seed=1), 2).pair_mode  # multi-GPU
-    assert plan.plan_pack(random_problem(1200, len1=200, len2_range=(10, 100), seed=1)).pair_mode
+    assert plan.plan_pack(random_problem(1200, len1=200, len2_range=(10, 100), seed=1)).mode in ("pair", "stream")
     with pytest.raises(NativeError) as e:
         plan.plan_pack(random_problem(4, len1=200, len2_range=(10, 100), weights=(70000, 1, 1, 1), seed=1), mode="pair")
     assert e.value.code == SA_ERR_UNSUPPORTED
     with pytest.raises(NativeError):  # profile of a 3000-row pair cannot fit in shared memory
         plan.plan_pack(random_problem(2, len1=4000, len2_range=(3000, 3000), seed=1), mode="pair")
+
+
+# ---- STREAM mode (warp-autonomous u16x2): planning + emulation
+
+@pytest.mark.parametrize("i", [1, 2, 3, 4, 5, 6])
+def test_stream_mode_walk_matches_golden(shipped_inputs, i):
+    path, gold = shipped_inputs[i]
+    blob = plan.plan_pack(Problem.from_file(path), 1, mode="stream")
+    assert blob.stream_mode and blob.header.npairs == (Problem.from_file(path).nseq + 1) // 2
+    assert format_results(plan.execute_blob_cpu(blob)) == gold.read_bytes()
+
+
+@pytest.mark.parametrize("seq1,seqs", EDGE)
+def test_stream_mode_edge_shapes(seq1, seqs):
+    p = Problem.from_parts((5, 1, 2, 3), seq1, seqs)
+    assert np.array_equal(plan.execute_blob_cpu(plan.plan_pack(p, 1, mode="stream")), solve_cpu(p, "naive"))
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_stream_mode_random(seed):
+    rng = np.random.default_rng(500 + seed)
+    w = tuple(int(x) for x in rng.integers(-3, 14, size=4))
+    len1 = int(rng.integers(30, 1300))
+    p = random_problem(9, len1=len1, len2_range=(1, min(len1 + 2, 1200)), weights=w, seed=seed)
+    assert np.array_equal(plan.execute_blob_cpu(plan.plan_pack(p, 1, mode="stream")), solve_cpu(p, "fast"))
+
+
+def test_auto_prefers_stream_then_pair_then_tile():
+    ok = random_problem(1200, len1=600, len2_range=(10, 500), weights=(10, 2, 3, 4), seed=1)
+    assert plan.plan_pack(ok).mode == "stream"
+    heavy = random_problem(1200, len1=600, len2_range=(10, 500), weights=(200, 2, 3, 4), seed=1)  # 512 rows x 204 > 32767
+    assert plan.plan_pack(heavy).mode == "pair"
+    with pytest.raises(NativeError):
+        plan.plan_pack(heavy, mode="stream")
+    huge = random_problem(1200, len1=600, len2_range=(10, 500), weights=(40000, 2, 3, 4), seed=1)
+    assert plan.plan_pack(huge).mode == "tile"
