@@ -20,6 +20,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <numeric>
+#include <thread>
 
 #include "core.hpp"
 
@@ -40,6 +41,24 @@ constexpr int32_t kNeg = -(1 << 30);  // "minus infinity" that survives one addi
 constexpr uint32_t kMergeCellsTile = 3, kMergeCellsPair = 10;
 
 inline uint32_t round_up(uint32_t v, uint32_t m) { return (v + m - 1) / m * m; }
+
+// Static split of [0, n) over host threads when the job is big enough to pay for them (the
+// reference's only OpenMP use is also input preparation, main.c:82,96 — there it races on stdin).
+template <typename F>
+void parallel_for(uint32_t n, uint64_t work_bytes, F fn) {
+    unsigned nt = work_bytes < (4u << 20) ? 1u : std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+    if (nt > n) nt = n ? n : 1u;
+    if (nt <= 1) {
+        fn(0u, n);
+        return;
+    }
+    std::vector<std::thread> pool;
+    for (unsigned t = 0; t < nt; ++t) {
+        const uint32_t a = (uint32_t)((uint64_t)n * t / nt), b = (uint32_t)((uint64_t)n * (t + 1) / nt);
+        pool.emplace_back([=]() { fn(a, b); });
+    }
+    for (auto& th : pool) th.join();
+}
 
 struct SeqPlan {
     uint32_t len = 0;
@@ -348,7 +367,7 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
 
     // ---- fill
     unsigned char* base = static_cast<unsigned char*>(dst);
-    std::memset(base, 0, total);
+    std::memset(base, 0, off_seq2);  // header + tables + Seq1; every Seq2 slot zeroes its own padding below
     sa_blob_header* h = reinterpret_cast<sa_blob_header*>(base);
     h->magic = SA_BLOB_MAGIC;
     h->version = SA_BLOB_VERSION;
@@ -384,18 +403,23 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     build_lut(al, p->weights, reinterpret_cast<int32_t*>(base + off_lut));
     for (uint32_t j = 0; j < len1; ++j) base[off_seq1 + j] = (unsigned char)(al.code[(unsigned char)p->seq1[j]] * 4);
     sa_seq_desc* tab = reinterpret_cast<sa_seq_desc*>(base + off_seqtab);
-    for (uint32_t s = 0; s < nseq; ++s) {
-        const SeqPlan& sp = plans[s];
-        tab[s].off = seq_off[s];
-        tab[s].len = (uint16_t)sp.len;
-        tab[s].ndiag = sp.ndiag;
-        tab[s].ntiles = (uint16_t)sp.ntiles;
-        tab[s].wd_log2 = (uint8_t)sp.wd_log2;
-        tab[s].home = home[s];
-        tab[s].crow = (uint16_t)sp.crow;
-        const std::string& q = p->seq2[s];
-        for (size_t i = 0; i < q.size(); ++i) base[seq_off[s] + i] = (unsigned char)al.code[(unsigned char)q[i]];
-    }
+    parallel_for(nseq, total, [&](uint32_t s0, uint32_t s1) {
+        for (uint32_t s = s0; s < s1; ++s) {
+            const SeqPlan& sp = plans[s];
+            tab[s].off = seq_off[s];
+            tab[s].len = (uint16_t)sp.len;
+            tab[s].ndiag = sp.ndiag;
+            tab[s].ntiles = (uint16_t)sp.ntiles;
+            tab[s].wd_log2 = (uint8_t)sp.wd_log2;
+            tab[s].home = home[s];
+            tab[s].crow = (uint16_t)sp.crow;
+            const std::string& q = p->seq2[s];
+            unsigned char* dstq = base + seq_off[s];
+            for (size_t i = 0; i < q.size(); ++i) dstq[i] = (unsigned char)al.code[(unsigned char)q[i]];
+            const size_t slot = (s + 1 < nseq ? seq_off[s + 1] : total) - seq_off[s];
+            std::memset(dstq + q.size(), 0, slot - q.size());
+        }
+    });
     sa_item* items = reinterpret_cast<sa_item*>(base + off_items);
     uint32_t w = 0;
     for (int r = 0; r < world; ++r) {

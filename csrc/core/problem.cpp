@@ -10,7 +10,11 @@
 #include <cstdio>
 #include <cstring>
 #include <limits>
+#include <algorithm>
+#include <array>
 #include <new>
+#include <thread>
+#include <vector>
 
 #include "core.hpp"
 
@@ -96,27 +100,47 @@ const Groups& groups() {
 
 Alphabet build_alphabet(const sa_problem& p) {
     Alphabet al;
-    for (int i = 0; i < 256; ++i) al.code[i] = -2;  // -2 = not seen yet
+    for (int i = 0; i < 256; ++i) al.code[i] = -2;  // -2 = does not occur
     std::memset(al.byte_of, 0, sizeof(al.byte_of));
     for (int c = 0; c < 26; ++c) {
         al.code['A' + c] = (int16_t)(1 + c);
         al.byte_of[1 + c] = (unsigned char)('A' + c);
     }
-    auto visit = [&](const std::string& s) {
-        for (unsigned char b : s) {
-            if (al.code[b] != -2) continue;
-            if (al.used < SA_ALPHABET) {
-                al.code[b] = (int16_t)al.used;
-                al.byte_of[al.used] = b;
-                ++al.used;
-            } else {
-                al.code[b] = -1;
-                al.ok = false;
-            }
-        }
+    // which bytes occur at all (threads for big inputs; the answer does not depend on the split)
+    const size_t n = p.seq2.size();
+    size_t bytes = p.seq1.size();
+    for (const auto& s : p.seq2) bytes += s.size();
+    unsigned nt = bytes < (4u << 20) ? 1u : std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+    std::vector<std::array<bool, 256>> seen(nt);
+    for (auto& a : seen) a.fill(false);
+    auto scan = [&](unsigned t) {
+        auto& mine = seen[t];
+        if (t == 0)
+            for (unsigned char b : p.seq1) mine[b] = true;
+        for (size_t i = n * t / nt; i < n * (t + 1) / nt; ++i)
+            for (unsigned char b : p.seq2[i]) mine[b] = true;
     };
-    visit(p.seq1);
-    for (const auto& s : p.seq2) visit(s);
+    if (nt == 1) {
+        scan(0);
+    } else {
+        std::vector<std::thread> pool;
+        for (unsigned t = 0; t < nt; ++t) pool.emplace_back(scan, t);
+        for (auto& th : pool) th.join();
+    }
+    // non-letter bytes get the spare codes 27..31 in increasing byte order
+    for (int b = 0; b < 256; ++b) {
+        bool present = false;
+        for (unsigned t = 0; t < nt; ++t) present = present || seen[t][(size_t)b];
+        if (!present || al.code[b] != -2) continue;
+        if (al.used < SA_ALPHABET) {
+            al.code[b] = (int16_t)al.used;
+            al.byte_of[al.used] = (unsigned char)b;
+            ++al.used;
+        } else {
+            al.code[b] = -1;
+            al.ok = false;
+        }
+    }
     return al;
 }
 

@@ -1247,15 +1247,23 @@ int sa_session_solve(sa_session* s, const sa_problem* prob, int32_t* out3) {
         return SA_ERR_ARG;
     }
     SA_CUDA_TRY(cudaSetDevice(s->device));
-    size_t need = 0;
-    int rc = sa_plan_pack_into(prob, 1, nullptr, 0, &need);
-    if (rc != SA_OK) return rc;
     const size_t nseq = (size_t)sa_problem_nseq(prob);
     if (nseq == 0) return SA_OK;
-    rc = session_reserve(s, need, nseq);
-    if (rc != SA_OK) return rc;
+    // plan + pack once, straight into the pinned buffer; only a buffer that turns out too small
+    // costs a second pass
     size_t got = 0;
-    rc = sa_plan_pack_into(prob, 1, s->h_in, s->h_in_cap, &got);
+    int rc = s->h_in ? sa_plan_pack_into(prob, 1, s->h_in, s->h_in_cap, &got) : SA_ERR_SMALL_BUFFER;
+    if (rc == SA_ERR_SMALL_BUFFER) {
+        if (!s->h_in) {
+            rc = sa_plan_pack_into(prob, 1, nullptr, 0, &got);
+            if (rc != SA_OK) return rc;
+        }
+        rc = session_reserve(s, got, nseq);
+        if (rc != SA_OK) return rc;
+        rc = sa_plan_pack_into(prob, 1, s->h_in, s->h_in_cap, &got);
+    }
+    if (rc != SA_OK) return rc;
+    rc = session_reserve(s, got, nseq);
     if (rc != SA_OK) return rc;
     const sa_blob_header* h = reinterpret_cast<const sa_blob_header*>(s->h_in);
     // One DMA copy in; the finalising CTAs post their result rows straight into pinned host

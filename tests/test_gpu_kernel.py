@@ -194,3 +194,23 @@ def test_stream_mode_random_vs_oracle(solver, seed):
     p = random_problem(301, len1=len1, len2_range=(1, min(len1 + 3, 1200)), weights=w, seed=seed)
     blob = solver.pack(p, mode="stream")
     assert np.array_equal(solver.solve_packed(blob), solve_cpu(p, "fast"))
+
+
+# ---- PyTorch extension binding (torch.ops.seqalign.*)
+
+def test_torch_ops_binding(solver, shipped_inputs):
+    import torch
+
+    from mpi_openmp_cuda_b200.ops import torch_ext
+
+    ops = torch_ext.load()
+    p = Problem.from_file(shipped_inputs[3][0])
+    blob = plan.plan_pack(p)
+    d_blob = torch.from_numpy(blob.numpy()[: blob.nbytes].copy()).cuda()
+    header = torch.from_numpy(blob.numpy()[:256].copy())
+    scratch = torch.zeros(int(ops.scratch_bytes(blob.nseq)), dtype=torch.uint8, device="cuda")
+    for _ in range(2):
+        out = ops.solve_blob(d_blob, header, scratch)
+        assert np.array_equal(out.cpu().numpy()[:, :3], solve_cpu(p, "fast"))
+    text = shipped_inputs[1][0].read_bytes().decode("latin-1")
+    assert np.array_equal(ops.solve_text(text, 0).numpy(), solve_cpu(Problem.from_file(shipped_inputs[1][0]), "fast"))
