@@ -816,13 +816,25 @@ __global__ void __launch_bounds__(kThreads, 2) sa_score_stream_kernel(const KPar
         const unsigned char* wp = seq1s + n0 + d0;
         uint2 lw0 = *reinterpret_cast<const uint2*>(wp);
         for (uint32_t rb = 0; rb < rows; rb += SA_STREAM_ROW_BLOCK) {
-            // ---- private profile block: row u, lane = letter
-            const uint32_t ca = (uint32_t)gA[rb + lane] * SA_ALPHABET + lane;
-            const uint32_t cb = has_b ? (uint32_t)gB[rb + lane] * SA_ALPHABET + lane : lane;
-#pragma unroll 8
-            for (uint32_t u = 0; u < SA_STREAM_ROW_BLOCK; ++u) {
-                const uint32_t a = __shfl_sync(0xFFFFFFFFu, ca, u) - u + lane;  // code*32 + my letter
-                const uint32_t b = __shfl_sync(0xFFFFFFFFu, cb, u) - u + lane;
+            // ---- private profile block: row u, lane = letter. Every lane fetches the block's 32+32
+            // codes itself (4 broadcast LDG.128 served by L1) and picks row u's bytes with ALU ops:
+            // the load/store pipe is the busiest unit of this kernel, so no SHFL here.
+            uint32_t wa[8], wb[8];
+            {
+                const uint4 a0 = *reinterpret_cast<const uint4*>(gA + rb), a1 = *reinterpret_cast<const uint4*>(gA + rb + 16);
+                wa[0] = a0.x, wa[1] = a0.y, wa[2] = a0.z, wa[3] = a0.w, wa[4] = a1.x, wa[5] = a1.y, wa[6] = a1.z, wa[7] = a1.w;
+                if (has_b) {
+                    const uint4 b0 = *reinterpret_cast<const uint4*>(gB + rb), b1 = *reinterpret_cast<const uint4*>(gB + rb + 16);
+                    wb[0] = b0.x, wb[1] = b0.y, wb[2] = b0.z, wb[3] = b0.w, wb[4] = b1.x, wb[5] = b1.y, wb[6] = b1.z, wb[7] = b1.w;
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) wb[k] = 0u;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < (int)SA_STREAM_ROW_BLOCK; ++u) {
+                const uint32_t a = ((wa[u >> 2] >> (8 * (u & 3))) & 0xFFu) * SA_ALPHABET + lane;  // code*32 + my letter
+                const uint32_t b = ((wb[u >> 2] >> (8 * (u & 3))) & 0xFFu) * SA_ALPHABET + lane;
                 pw[u * SA_ALPHABET + lane] = lutlo[a] | luthi[b];
             }
             __syncwarp();
