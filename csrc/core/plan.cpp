@@ -154,28 +154,24 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
         SeqPlan g;
     };
     std::vector<Pair> pairs;
-    bool pair_ok = world == 1 && wrange <= 32767 && nvalid > 0;
-    std::string pair_why = world != 1 ? "pair mode is single-GPU" : (wrange > 32767 ? "weight range exceeds 16 bits" : "no sequence has candidates");
+    bool pair_ok = wrange <= 32767 && nvalid > 0 && (world == 1 || mode != SA_MODE_PAIR);
+    std::string pair_why = (world != 1 && mode == SA_MODE_PAIR) ? "PAIR mode is single-GPU (STREAM and TILE run on the fabric)"
+                                                                 : (wrange > 32767 ? "weight range exceeds 16 bits" : "no sequence has candidates");
     uint32_t pair_cols_needed = 0;
     const bool want_pairs = mode == SA_MODE_PAIR || mode == SA_MODE_STREAM || (mode == SA_MODE_AUTO && nvalid >= SA_PAIR_MIN_SEQS);
     bool stream_ok = pair_ok && mode != SA_MODE_PAIR;
     std::string stream_why = pair_why;
+    std::vector<uint32_t> order;  // scorable sequences, longest first; neighbours become pairs
     if (pair_ok && want_pairs) {
-        std::vector<uint32_t> order;
         for (uint32_t s = 0; s < nseq; ++s)
             if (p->seq2[s].size() <= len1) order.push_back(s);
         std::stable_sort(order.begin(), order.end(),
                          [&](uint32_t x, uint32_t y) { return p->seq2[x].size() > p->seq2[y].size(); });
-        // STREAM needs every whole column of rows inside 16 bits
-        for (size_t i = 0; stream_ok && i < order.size(); i += 2)
-            if ((int64_t)round_up((uint32_t)p->seq2[order[i]].size(), SA_STREAM_ROW_BLOCK) * wrange > 32767) {
-                stream_ok = false;
-                stream_why = "a whole sequence would overflow 16 bits";
-            }
-        if (stream_ok && round_up(len1 + SA_SEQ1_TAIL_PAD, 16) > SA_STREAM_MAX_SEQ1) {
-            stream_ok = false;
-            stream_why = "Seq1 does not fit in shared memory next to the profile blocks";
-        }
+    }
+    // Fills `pairs` with the STREAM (one warp per tile, all rows) or PAIR (CTA per pair) geometry.
+    auto plan_pairs = [&](bool as_stream, std::string& why) -> bool {
+        pairs.clear();
+        pair_cols_needed = 0;
         for (size_t i = 0; i < order.size(); i += 2) {
             Pair pr;
             pr.a = order[i];
@@ -187,52 +183,73 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
             g.len = rows;
             g.ndiag = (int32_t)dmax;
             const uint32_t d = dmax == 0 ? 1u : dmax;
-            if (stream_ok) {
-                // one warp per (pair, 256-offset tile) walks every row in blocks of 32
+            if (as_stream) {
                 g.stream = true;
                 g.wd_log2 = 0;
                 g.crow = round_up(rows, SA_STREAM_ROW_BLOCK);
+                if ((int64_t)g.crow * wrange > 32767) {
+                    why = "a whole sequence would overflow 16 bits";
+                    return false;
+                }
                 g.ntiles = (d + kWarpDiag - 1) / kWarpDiag;
                 g.item_cost = (uint64_t)kWarpDiag * g.crow;  // per tile
-                pr.g = g;
-                pair_cols_needed = std::max(pair_cols_needed, g.ntiles * kWarpDiag + g.crow);
-                pairs.push_back(pr);
-                continue;
-            }
-            // PAIR geometry: as plan_sequence, with the row-chunk length also bounded by the u16 range
-            uint64_t best_cost = ~0ull;
-            for (uint32_t l = 0; (1u << l) <= kWarps; ++l) {
-                const uint32_t wd = 1u << l, wr = kWarps / wd;
-                const uint32_t crow = round_up((rows + wr - 1) / wr, kU);
-                if ((int64_t)crow * wrange > 32767) continue;
-                const uint32_t tn = kWarpDiag * wd, ntiles = (d + tn - 1) / tn;
-                const uint64_t cost = (uint64_t)ntiles * tn * wr * (crow + kMergeCellsPair);
-                if (cost < best_cost) {
-                    best_cost = cost;
-                    g.wd_log2 = l;
-                    g.crow = crow;
-                    g.ntiles = ntiles;
-                    g.item_cost = (uint64_t)ntiles * tn * wr * crow;  // whole pair, scan cells only
+            } else {
+                uint64_t best_cost = ~0ull;
+                for (uint32_t l = 0; (1u << l) <= kWarps; ++l) {
+                    const uint32_t wd = 1u << l, wr = kWarps / wd;
+                    const uint32_t crow = round_up((rows + wr - 1) / wr, kU);
+                    if ((int64_t)crow * wrange > 32767) continue;
+                    const uint32_t tn = kWarpDiag * wd, ntiles = (d + tn - 1) / tn;
+                    const uint64_t cost = (uint64_t)ntiles * tn * wr * (crow + kMergeCellsPair);
+                    if (cost < best_cost) {
+                        best_cost = cost;
+                        g.wd_log2 = l;
+                        g.crow = crow;
+                        g.ntiles = ntiles;
+                        g.item_cost = (uint64_t)ntiles * tn * wr * crow;  // whole pair, scan cells only
+                    }
                 }
-            }
-            if (best_cost == ~0ull) {
-                pair_ok = false;
-                pair_why = "a row chunk would overflow 16 bits";
-                break;
+                if (best_cost == ~0ull) {
+                    why = "a row chunk would overflow 16 bits";
+                    return false;
+                }
             }
             pr.g = g;
             pair_cols_needed = std::max(pair_cols_needed, g.ntiles * (kWarpDiag << g.wd_log2) + g.rows_padded());
             pairs.push_back(pr);
         }
-        if (pair_ok && !stream_ok) {
+        if (as_stream) {
+            if (round_up(std::max(len1 + SA_SEQ1_TAIL_PAD, pair_cols_needed + 16u), 16) > SA_STREAM_MAX_SEQ1) {
+                why = "Seq1 does not fit in shared memory next to the profile blocks";
+                return false;
+            }
+        } else {
             uint32_t mr = kU;
             for (const Pair& pr : pairs) mr = std::max(mr, pr.g.rows_padded());
             const uint64_t smem = (uint64_t)mr * 128 + 2ull * round_up(mr, 16) +
                                   round_up(std::max(len1 + SA_SEQ1_TAIL_PAD, pair_cols_needed + 16u), 16) + SA_PAIR_FIXED_SMEM;
             if (smem > SA_PAIR_MAX_SMEM) {
-                pair_ok = false;
-                pair_why = "pair profile does not fit in shared memory";
+                why = "pair profile does not fit in shared memory";
+                return false;
             }
+        }
+        return true;
+    };
+    if (pair_ok && want_pairs) {
+        if (stream_ok) stream_ok = plan_pairs(true, stream_why);
+        if (stream_ok && mode == SA_MODE_AUTO) {
+            // A STREAM item keeps one warp busy for a long time; with fewer than a few items per resident
+            // warp the tail dominates (measured: 2048 sequences per GPU run 25% slower than TILE).
+            uint64_t n_items = 0;
+            for (const Pair& pr : pairs) n_items += pr.g.ntiles;
+            if (n_items < (uint64_t)SA_STREAM_MIN_ITEMS_PER_GPU * (uint64_t)world) {
+                stream_ok = false;
+                stream_why = "too few items per GPU for warp-autonomous tiles";
+            }
+        }
+        if (!stream_ok) {
+            if (world == 1 && mode != SA_MODE_STREAM) pair_ok = plan_pairs(false, pair_why);
+            else pair_ok = false;  // the fabric kernel runs TILE or STREAM items only
         }
     } else if (pair_ok) {
         pair_ok = false;
@@ -333,8 +350,15 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     if (use_pairs) {
         std::stable_sort(pairs.begin(), pairs.end(), [](const Pair& x, const Pair& y) { return x.g.item_cost > y.g.item_cost; });
         if (use_stream) {
-            for (uint32_t pid = 0; pid < pairs.size(); ++pid)
-                for (uint32_t t = 0; t < pairs[pid].g.ntiles; ++t) per_rank[0].push_back({pid, t});
+            // whole pairs are dealt to the least-loaded rank, costliest first: every atomic stays local
+            std::vector<uint64_t> load((size_t)world, 0);
+            for (uint32_t pid = 0; pid < pairs.size(); ++pid) {
+                const int r = (int)(std::min_element(load.begin(), load.end()) - load.begin());
+                home[pairs[pid].a] = (uint8_t)r;
+                if (pairs[pid].b != SA_NO_SEQ) home[pairs[pid].b] = (uint8_t)r;
+                for (uint32_t t = 0; t < pairs[pid].g.ntiles; ++t) per_rank[(size_t)r].push_back({pid, t});
+                load[(size_t)r] += pairs[pid].g.item_cost * pairs[pid].g.ntiles;
+            }
         } else {
             for (const Pair& pr : pairs) per_rank[0].push_back({pr.a, pr.b});
         }

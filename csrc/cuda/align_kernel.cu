@@ -195,44 +195,17 @@ __device__ __forceinline__ int first_k_on_diagonal(const int* lut_i, const unsig
 
 // ------------------------------------------------------------------ the kernel
 
-// kFabric = false: one GPU owns everything (p.key/p.cnt/p.out/p.ctrl are local).
-// kFabric = true : one of `world` cooperating launches, one per GPU (see sa_cuda_fabric_solve):
-//   rank 0 broadcasts the blob from inside the kernel (NVLS multicast store or per-peer P2P stores,
-//   chunk by chunk, each chunk followed by a release flag), the other ranks start scoring as soon
-//   as the chunks they need have landed; per-sequence keys/counters live on the sequence's home
-//   rank and are updated with system-scope atomics over NVLink; results go straight into rank 0's
-//   table; the last CTA of every rank bumps rank 0's arrival counter and rank 0's last CTA waits
-//   for all of them. No MPI/NCCL call on either path (replaces main.c:149-152,174,195-197).
-template <bool kFabric>
-__device__ __forceinline__ void score_body(const KParams& p) {
-    extern __shared__ __align__(16) unsigned char smem[];
-    unsigned char* const lut_b = smem;
-    unsigned char* const s2 = lut_b + kLutBytes;
-    unsigned char* const win = s2 + p.s2_cap;
-    int* const csum = reinterpret_cast<int*>(win + p.win_cap);
-    int* const cmax = csum + kSumWords;
-    unsigned long long* const red = reinterpret_cast<unsigned long long*>(cmax + kMaxWords);  // [kWarps]
-    unsigned long long* const mbar = red + kWarps;
-    int* const scan = reinterpret_cast<int*>(mbar + 1);  // [kWarps]
-    uint32_t* const ctl = reinterpret_cast<uint32_t*>(scan + kWarps);  // [0] item, [1] last flag, [2] first k
+// Shared by every fabric launch: set when one of this CTA's bounded cross-GPU waits timed out.
+__shared__ uint32_t s_abort;
 
-    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+// Fabric prologue, once per CTA (requires a preceding __syncthreads after s_abort = 0):
+// rank 0 pushes its share of the blob's chunks to every peer and publishes their flags; the other
+// ranks wait until the chunks holding header, table, Seq1, descriptors and items have landed.
+__device__ __forceinline__ void fabric_prologue(const KParams& p) {
+    constexpr bool kFabric = true;
+    const uint32_t tid = threadIdx.x;
     const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
-    if (!kFabric && hdr->magic != SA_BLOB_MAGIC) return;  // never walk memory that is not a packed problem
-    const uint32_t bar = smem_u32(mbar);
-    uint32_t parity = 0;
-    uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
-    unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
-    const bool timeline = kFabric && p.timeline != 0u;
-    if (timeline && tid == 0) atomicMin(&times[0], global_ns());
-
-    if (tid == 0) {
-        mbar_init(bar, 1);
-        mbar_fence_init();
-        ctl[3] = 0u;  // abort flag
-    }
-    __syncthreads();
-
+    uint32_t* const my_ctl = reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl);
     if (kFabric && p.world > 1) {
         if (p.rank == 0) {
             // ---- broadcast, fused with scoring: each CTA pushes its share of chunks, then scores
@@ -270,7 +243,7 @@ __device__ __forceinline__ void score_body(const KParams& p) {
                     for (uint32_t c = 1; ok && c < npre; ++c) ok = wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns);
                 }
                 if (!ok) {
-                    ctl[3] = 1u;
+                    s_abort = 1u;
                     atomicExch(my_ctl + kCtlError, 1u);
                 }
                 fence_proxy_async();
@@ -278,7 +251,88 @@ __device__ __forceinline__ void score_body(const KParams& p) {
             __syncthreads();
         }
     }
-    const bool dead_on_arrival = kFabric && ctl[3] != 0u;
+}
+
+// Launch epilogue, once per CTA after its last item: the last CTA of the launch re-arms the work
+// queue; in a fabric launch it also tells rank 0 that this rank has delivered, and rank 0's last CTA
+// waits (bounded) for every rank.
+template <bool kFabric>
+__device__ __forceinline__ void launch_epilogue(const KParams& p) {
+    const uint32_t tid = threadIdx.x;
+    uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
+    unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
+    const bool timeline = kFabric && p.timeline != 0u;
+    // Last CTA out re-arms the work queue for the next launch.
+    if (tid == 0) {
+        if (timeline) atomicMax(&times[2], global_ns());
+        if (kFabric) __threadfence_system(); else __threadfence();
+        const unsigned int done = atomicAdd(&my_ctl[kCtlCtasDone], 1u);
+        if (done + 1u == gridDim.x) {
+            my_ctl[kCtlNext] = 0u;
+            my_ctl[kCtlCtasDone] = 0u;
+            if (kFabric && p.world > 1) {
+                // Gather: everything this rank produced is already in rank 0's table; tell rank 0.
+                uint32_t* const arrived = reinterpret_cast<uint32_t*>(p.peer[0] + p.off_ctrl) + kCtlRanksDone;
+                __threadfence_system();
+                atomicAdd_system(arrived, 1u);
+                if (timeline) times[3] = global_ns();
+                if (p.rank == 0) {  // the launch on rank 0 ends only when every rank has delivered
+                    const unsigned long long t0 = global_ns();
+                    while (ld_acquire_sys(arrived) < p.world) {
+                        __nanosleep(128);
+                        if (global_ns() - t0 > p.timeout_ns) {
+                            atomicExch(my_ctl + kCtlError, 2u);
+                            break;
+                        }
+                    }
+                    *arrived = 0u;
+                    if (timeline) times[4] = global_ns();
+                }
+            }
+        }
+    }
+}
+
+// kFabric = false: one GPU owns everything (p.key/p.cnt/p.out/p.ctrl are local).
+// kFabric = true : one of `world` cooperating launches, one per GPU (see sa_cuda_fabric_solve):
+//   rank 0 broadcasts the blob from inside the kernel (NVLS multicast store or per-peer P2P stores,
+//   chunk by chunk, each chunk followed by a release flag), the other ranks start scoring as soon
+//   as the chunks they need have landed; per-sequence keys/counters live on the sequence's home
+//   rank and are updated with system-scope atomics over NVLink; results go straight into rank 0's
+//   table; the last CTA of every rank bumps rank 0's arrival counter and rank 0's last CTA waits
+//   for all of them. No MPI/NCCL call on either path (replaces main.c:149-152,174,195-197).
+template <bool kFabric>
+__device__ __forceinline__ void score_body(const KParams& p, const bool prologue_done = false, const bool epilogue_later = false) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    unsigned char* const lut_b = smem;
+    unsigned char* const s2 = lut_b + kLutBytes;
+    unsigned char* const win = s2 + p.s2_cap;
+    int* const csum = reinterpret_cast<int*>(win + p.win_cap);
+    int* const cmax = csum + kSumWords;
+    unsigned long long* const red = reinterpret_cast<unsigned long long*>(cmax + kMaxWords);  // [kWarps]
+    unsigned long long* const mbar = red + kWarps;
+    int* const scan = reinterpret_cast<int*>(mbar + 1);  // [kWarps]
+    uint32_t* const ctl = reinterpret_cast<uint32_t*>(scan + kWarps);  // [0] item, [1] last flag, [2] first k
+
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
+    if (!kFabric && hdr->magic != SA_BLOB_MAGIC) return;  // never walk memory that is not a packed problem
+    const uint32_t bar = smem_u32(mbar);
+    uint32_t parity = 0;
+    uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
+    unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
+    const bool timeline = kFabric && p.timeline != 0u;
+    if (timeline && tid == 0) atomicMin(&times[0], global_ns());
+
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        mbar_fence_init();
+        if (!prologue_done) s_abort = 0u;
+    }
+    __syncthreads();
+
+    if (kFabric && !prologue_done) fabric_prologue(p);
+    const bool dead_on_arrival = kFabric && s_abort != 0u;
     if (timeline && tid == 0) atomicMax(&times[1], global_ns());
 
     const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + (dead_on_arrival ? 0u : hdr->off_seqtab));
@@ -314,7 +368,7 @@ __device__ __forceinline__ void score_body(const KParams& p) {
                 bool ok = true;
                 for (uint32_t c = c0; ok && c <= c1; ++c) ok = wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns);
                 if (!ok) {
-                    ctl[3] = 1u;
+                    s_abort = 1u;
                     atomicExch(my_ctl + kCtlError, 1u);
                 }
                 fence_proxy_async();
@@ -323,7 +377,7 @@ __device__ __forceinline__ void score_body(const KParams& p) {
         }
         __syncthreads();  // also: every read of s2/win/csum of the previous item is done
         const uint32_t item = ctl[0];
-        if (item >= item_end || (kFabric && ctl[3] != 0u)) break;
+        if (item >= item_end || (kFabric && s_abort != 0u)) break;
 
         const uint32_t seq = items[item].seq, tile = items[item].tile;
         const sa_seq_desc sd = seqtab[seq];
@@ -459,39 +513,10 @@ __device__ __forceinline__ void score_body(const KParams& p) {
         }
     }
 
-    // Last CTA out re-arms the work queue for the next launch.
-    if (tid == 0) {
-        if (timeline) atomicMax(&times[2], global_ns());
-        if (kFabric) __threadfence_system(); else __threadfence();
-        const unsigned int done = atomicAdd(&my_ctl[kCtlCtasDone], 1u);
-        if (done + 1u == gridDim.x) {
-            my_ctl[kCtlNext] = 0u;
-            my_ctl[kCtlCtasDone] = 0u;
-            if (kFabric && p.world > 1) {
-                // Gather: everything this rank produced is already in rank 0's table; tell rank 0.
-                uint32_t* const arrived = reinterpret_cast<uint32_t*>(p.peer[0] + p.off_ctrl) + kCtlRanksDone;
-                __threadfence_system();
-                atomicAdd_system(arrived, 1u);
-                if (timeline) times[3] = global_ns();
-                if (p.rank == 0) {  // the launch on rank 0 ends only when every rank has delivered
-                    const unsigned long long t0 = global_ns();
-                    while (ld_acquire_sys(arrived) < p.world) {
-                        __nanosleep(128);
-                        if (global_ns() - t0 > p.timeout_ns) {
-                            atomicExch(my_ctl + kCtlError, 2u);
-                            break;
-                        }
-                    }
-                    *arrived = 0u;
-                    if (timeline) times[4] = global_ns();
-                }
-            }
-        }
-    }
+    if (!epilogue_later) launch_epilogue<kFabric>(p);
 }
 
 __global__ void __launch_bounds__(kThreads, 2) sa_score_kernel(const KParams p) { score_body<false>(p); }
-__global__ void __launch_bounds__(kThreads, 2) sa_score_fabric_kernel(const KParams p) { score_body<true>(p); }
 
 // ------------------------------------------------------------------ PAIR mode kernel
 //
@@ -749,10 +774,11 @@ __device__ __forceinline__ int warp_first_k(const uint32_t* lutlo, const unsigne
     return (int)mine;
 }
 
-__global__ void __launch_bounds__(kThreads, 2) sa_score_stream_kernel(const KParams p) {
+template <bool kFabric>
+__device__ __forceinline__ void stream_body(const KParams& p, const bool epilogue_later = false) {
     extern __shared__ __align__(16) unsigned char smem[];
     const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
-    if (hdr->magic != SA_BLOB_MAGIC) return;  // never walk memory that is not a packed problem
+    if (!kFabric && hdr->magic != SA_BLOB_MAGIC) return;  // never walk memory that is not a packed problem
     const uint32_t seq1_bytes = (hdr->len1_padded + 15u) & ~15u;
     uint32_t* const lutlo = reinterpret_cast<uint32_t*>(smem);
     uint32_t* const luthi = lutlo + SA_ALPHABET * SA_ALPHABET;
@@ -767,10 +793,14 @@ __global__ void __launch_bounds__(kThreads, 2) sa_score_stream_kernel(const KPar
     const int vmin = hdr->value_min;
     constexpr uint32_t BIG = 32767u, BIG2 = BIG | (BIG << 16);
     const uint32_t bar = smem_u32(mbar);
+    uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
+    int4* const out = kFabric ? reinterpret_cast<int4*>(p.peer[0] + p.off_out) : p.out;
+    const uint32_t item_begin = kFabric ? hdr->rank_first_item[p.rank] : p.item_begin;
+    const uint32_t item_end = kFabric ? hdr->rank_first_item[p.rank + 1] : p.item_end;
 
     if (p.write_empty) {
         for (uint32_t s = blockIdx.x * kThreads + tid; s < hdr->nseq; s += gridDim.x * kThreads)
-            if (seqtab[s].ntiles == 0) p.out[s] = make_int4(INT_MIN, 0, 0, 0);
+            if (seqtab[s].ntiles == 0) out[s] = make_int4(INT_MIN, 0, 0, 0);
     }
     if (tid == 0) {
         mbar_init(bar, 1);
@@ -795,9 +825,9 @@ __global__ void __launch_bounds__(kThreads, 2) sa_score_stream_kernel(const KPar
     const uint32_t d0 = lane * kR;
     for (;;) {
         uint32_t item = 0;
-        if (lane == 0) item = p.item_begin + atomicAdd(&p.ctrl[kCtlNext], 1u);
+        if (lane == 0) item = item_begin + atomicAdd(&my_ctl[kCtlNext], 1u);
         item = __shfl_sync(0xFFFFFFFFu, item, 0);
-        if (item >= p.item_end) break;
+        if (item >= item_end || (kFabric && *reinterpret_cast<volatile uint32_t*>(&s_abort) != 0u)) break;
         const uint32_t pid = items[item].seq, tile = items[item].tile;
         const uint32_t ia = pairs[pid].seq, ib = pairs[pid].tile;
         const bool has_b = ib != SA_NO_SEQ;
@@ -807,6 +837,23 @@ __global__ void __launch_bounds__(kThreads, 2) sa_score_stream_kernel(const KPar
         const uint32_t rows = da.crow, n0 = tile * SA_DIAG_PER_WARP;
         const unsigned char* const gA = p.blob + da.off;
         const unsigned char* const gB = p.blob + db.off;
+        unsigned long long* const keyA_p = (kFabric ? reinterpret_cast<unsigned long long*>(p.peer[da.home] + p.off_key) : p.key) + ia;
+        unsigned long long* const keyB_p = (kFabric ? reinterpret_cast<unsigned long long*>(p.peer[da.home] + p.off_key) : p.key) + (has_b ? ib : ia);
+        unsigned int* const cnt_p = (kFabric ? reinterpret_cast<unsigned int*>(p.peer[da.home] + p.off_cnt) : p.cnt) + pid;
+        if (kFabric && p.rank != 0) {  // the two sequences' letters may still be in flight from rank 0
+            uint32_t ok = 1u;
+            if (lane == 0) {
+                const uint32_t cb = hdr->chunk_bytes;
+                for (uint32_t c = da.off / cb; ok && c <= (da.off + rows - 1u) / cb; ++c) ok = wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns);
+                if (has_b)
+                    for (uint32_t c = db.off / cb; ok && c <= (db.off + rows - 1u) / cb; ++c) ok = wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns);
+                if (!ok) {
+                    *reinterpret_cast<volatile uint32_t*>(&s_abort) = 1u;
+                    atomicExch(my_ctl + kCtlError, 1u);
+                }
+            }
+            if (!__shfl_sync(0xFFFFFFFFu, ok, 0)) break;
+        }
 
         uint32_t P[kR + 1], best[kR];
 #pragma unroll
@@ -893,42 +940,65 @@ __global__ void __launch_bounds__(kThreads, 2) sa_score_stream_kernel(const KPar
         }
         uint32_t last = 0;
         if (lane == 0) {
-            atomicMax(&p.key[ia], keyA);
-            if (has_b) atomicMax(&p.key[ib], keyB);
-            __threadfence();
-            last = (atomicAdd(&p.cnt[pid], 1u) + 1u == da.ntiles) ? 1u : 0u;
+            if (kFabric) {
+                atomicMax_system(keyA_p, keyA);
+                if (has_b) atomicMax_system(keyB_p, keyB);
+                if (da.home == p.rank) __threadfence(); else __threadfence_system();
+                last = (atomicAdd_system(cnt_p, 1u) + 1u == da.ntiles) ? 1u : 0u;
+            } else {
+                atomicMax(keyA_p, keyA);
+                if (has_b) atomicMax(keyB_p, keyB);
+                __threadfence();
+                last = (atomicAdd(cnt_p, 1u) + 1u == da.ntiles) ? 1u : 0u;
+            }
         }
         last = __shfl_sync(0xFFFFFFFFu, last, 0);
         if (last) {  // this warp delivered the pair's last tile: finish both sequences
             for (int half = 0; half < (has_b ? 2 : 1); ++half) {
                 const sa_seq_desc& sd = half == 0 ? da : db;
                 const uint32_t sidx = half == 0 ? ia : ib;
+                unsigned long long* const kp = half == 0 ? keyA_p : keyB_p;
                 unsigned long long fk = 0ull;
                 if (lane == 0) {
-                    __threadfence();
-                    fk = atomicMax(&p.key[sidx], 0ull);
+                    if (kFabric) {
+                        __threadfence_system();
+                        fk = atomicMax_system(kp, 0ull);
+                    } else {
+                        __threadfence();
+                        fk = atomicMax(kp, 0ull);
+                    }
                 }
                 fk = __shfl_sync(0xFFFFFFFFu, fk, 0);
                 const int bestv = (int)((uint32_t)(fk >> 32) ^ 0x80000000u);
                 const uint32_t nwin = 0xFFFFFFFFu - (uint32_t)(fk & 0xFFFFFFFFull);
                 const int kres = sd.ndiag == 0 ? 0 : warp_first_k(lutlo, half == 0 ? gA : gB, seq1s + nwin, sd.len, bestv, vmin, lane);
                 if (lane == 0) {
-                    p.out[sidx] = make_int4(bestv, (int)nwin, kres, 0);
-                    p.key[sidx] = 0ull;
+                    out[sidx] = make_int4(bestv, (int)nwin, kres, 0);
+                    *kp = 0ull;
                 }
             }
-            if (lane == 0) p.cnt[pid] = 0u;
+            if (lane == 0) *cnt_p = 0u;
         }
     }
     __syncthreads();
-    if (tid == 0) {
-        __threadfence();
-        const unsigned int done = atomicAdd(&p.ctrl[kCtlCtasDone], 1u);
-        if (done + 1u == gridDim.x) {
-            p.ctrl[kCtlNext] = 0u;
-            p.ctrl[kCtlCtasDone] = 0u;
-        }
-    }
+    if (!epilogue_later) launch_epilogue<kFabric>(p);
+}
+
+__global__ void __launch_bounds__(kThreads, 2) sa_score_stream_kernel(const KParams p) { stream_body<false>(p); }
+
+// One fabric kernel for both modes: ranks other than 0 launch before they know anything about
+// the problem, so the mode is read from the blob header once the broadcast prefix has landed.
+__global__ void __launch_bounds__(kThreads, 2) sa_score_fabric_kernel(const KParams p) {
+    if (threadIdx.x == 0) s_abort = 0u;
+    __syncthreads();
+    fabric_prologue(p);
+    __syncthreads();
+    const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
+    if (s_abort == 0u && (hdr->flags & SA_FLAG_STREAM_MODE))
+        stream_body<true>(p, true);
+    else
+        score_body<true>(p, true, true);
+    launch_epilogue<true>(p);
 }
 
 // ------------------------------------------------------------------ host side
@@ -1355,8 +1425,13 @@ int sa_cuda_fabric_solve(const sa_fabric_desc* f, const sa_blob_header* header, 
             sa_set_last_error("sa_cuda_fabric_solve: blob was planned for a different number of GPUs");
             return SA_ERR_ARG;
         }
+        if (header->flags & SA_FLAG_PAIR_MODE) {
+            sa_set_last_error("sa_cuda_fabric_solve: PAIR-mode blobs are single-GPU; plan with SA_MODE_AUTO, TILE or STREAM");
+            return SA_ERR_ARG;
+        }
         if (header->nseq > f->layout.max_seq || header->total_bytes > f->layout.max_blob_bytes ||
-            header->nchunks > kMaxChunks || header->max_rows_padded > SA_GPU_MAX_SEQ2 + 128u) {
+            header->nchunks > kMaxChunks || header->max_rows_padded > SA_GPU_MAX_SEQ2 + 128u ||
+            ((header->flags & SA_FLAG_STREAM_MODE) && ((header->len1_padded + 15u) & ~15u) > SA_STREAM_MAX_SEQ1)) {
             sa_set_last_error("sa_cuda_fabric_solve: problem exceeds the capacity this fabric was created with");
             return SA_ERR_TOO_LARGE;
         }
@@ -1393,7 +1468,8 @@ int sa_cuda_fabric_solve(const sa_fabric_desc* f, const sa_blob_header* header, 
     // same input-independent shape: full persistent grid, shared memory for the largest sequence.
     p.s2_cap = (SA_GPU_MAX_SEQ2 + 128u + 15u) & ~15u;
     p.win_cap = (SA_GPU_MAX_SEQ2 + 128u + 4096u + 16u + 15u) & ~15u;
-    const uint32_t smem = smem_bytes_for(p.s2_cap, p.win_cap);
+    const uint32_t smem_stream = 2u * kLutBytes + SA_STREAM_MAX_SEQ1 + (uint32_t)kWarps * SA_STREAM_ROW_BLOCK * SA_ALPHABET * 4u + 64u;
+    const uint32_t smem = std::max(smem_bytes_for(p.s2_cap, p.win_cap), smem_stream);
     {
         std::lock_guard<std::mutex> lock(g_mu);
         if ((int)smem > di->smem_fabric_set) {

@@ -140,6 +140,7 @@ size_t sa_format(const int32_t* results, int32_t nseq, char* buf, size_t cap);
 #define SA_MODE_STREAM 3
 #define SA_FLAG_PAIR_MODE 1u
 #define SA_FLAG_STREAM_MODE 2u
+#define SA_STREAM_MIN_ITEMS_PER_GPU 16384u /* AUTO uses STREAM only with several items per resident warp */
 #define SA_STREAM_ROW_BLOCK 32u
 #define SA_STREAM_MAX_SEQ1 (24u << 10)  /* padded Seq1 bytes that may stay resident in shared memory */
 #define SA_NO_SEQ 0xFFFFFFFFu

@@ -169,6 +169,8 @@ def time_ours_distributed(problem, steps: int, warmup: int, large_problem=None):
         "padded_cells": int(blob.header.padded_cells), "nitems": blob.nitems,
         "fabric": {"multicast": fabric.use_multicast, "world": world},
         "large": large,
+        "large_mode": lblob.mode if large is not None else None,
+        "mode": blob.mode,
     }
     dist.destroy_process_group()
     return out

@@ -61,3 +61,16 @@ def test_more_gpus_byte_identical(shipped_inputs, world):
         out = _run(world, path)
         assert out.returncode == 0, out.stderr.decode()[-2000:]
         assert out.stdout == gold.read_bytes()
+
+
+def test_two_gpus_stream_mode_through_the_fabric():
+    """Large batch: the fabric kernel runs warp-autonomous STREAM items (whole pairs per rank)."""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    import os
+
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                          "127.0.0.1", "--master-port", "29733", str(ROOT / "tests" / "_fabric_stream_worker.py")],
+                         capture_output=True, cwd=ROOT, timeout=600, env=dict(os.environ, PYTHONPATH=str(ROOT)))
+    assert out.returncode == 0, out.stderr.decode()[-3000:]
+    assert b"stream fabric ok" in out.stdout

@@ -145,17 +145,24 @@ def test_pair_mode_random_vs_oracle(solver, seed):
 
 def test_auto_mode_picks_pairs_for_large_batches(solver):
     p = random_problem(2500, len1=1400, len2_range=(40, 1100), seed=31)
+    ref = solve_cpu(p, "fast")
+    blob = solver.pack(p)
+    assert blob.mode == "pair"
+    assert np.array_equal(solver.solve_packed(blob), ref)
+    assert np.array_equal(solver.solve(p), ref)  # native session, same auto choice
+    for mode in ("tile", "stream"):
+        b = solver.pack(p, mode=mode)
+        assert b.mode == mode
+        assert np.array_equal(solver.solve_packed(b), ref)
+
+
+def test_auto_mode_picks_stream_for_very_large_batches(solver):
+    p = random_problem(12000, len1=700, len2_range=(10, 120), seed=32)
     blob = solver.pack(p)
     assert blob.mode == "stream"
-    pair = solver.pack(p, mode="pair")
-    assert pair.mode == "pair"
-    assert np.array_equal(solver.solve_packed(pair), solve_cpu(p, "fast"))
-    blob = solver.pack(p)
-    assert np.array_equal(solver.solve_packed(blob), solve_cpu(p, "fast"))
-    assert np.array_equal(solver.solve(p), solve_cpu(p, "fast"))  # native session, same auto choice
-    tile = solver.pack(p, mode="tile")
-    assert not tile.pair_mode
-    assert np.array_equal(solver.solve_packed(tile), solve_cpu(p, "fast"))
+    ref = solve_cpu(p, "fast")
+    assert np.array_equal(solver.solve_packed(blob), ref)
+    assert np.array_equal(solver.solve(p), ref)
 
 
 def test_pair_mode_limits_fall_back_to_tiles(solver):

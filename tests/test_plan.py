@@ -177,11 +177,36 @@ def test_stream_mode_random(seed):
 
 
 def test_auto_prefers_stream_then_pair_then_tile():
+    big = random_problem(12000, len1=600, len2_range=(10, 100), weights=(10, 2, 3, 4), seed=1)
+    assert plan.plan_pack(big).mode == "stream"            # >= 16384 warp items
+    assert plan.plan_pack(big, 8).mode == "tile"           # ... but not per GPU on 8 GPUs
+    assert plan.plan_pack(big, 8, mode="stream").mode == "stream"
     ok = random_problem(1200, len1=600, len2_range=(10, 500), weights=(10, 2, 3, 4), seed=1)
-    assert plan.plan_pack(ok).mode == "stream"
+    assert plan.plan_pack(ok).mode == "pair"               # too few items for warp-autonomous tiles
+    assert plan.plan_pack(ok, mode="stream").mode == "stream"
     heavy = random_problem(1200, len1=600, len2_range=(10, 500), weights=(200, 2, 3, 4), seed=1)  # 512 rows x 204 > 32767
     assert plan.plan_pack(heavy).mode == "pair"
     with pytest.raises(NativeError):
         plan.plan_pack(heavy, mode="stream")
     huge = random_problem(1200, len1=600, len2_range=(10, 500), weights=(40000, 2, 3, 4), seed=1)
     assert plan.plan_pack(huge).mode == "tile"
+
+
+def test_stream_mode_partitions_whole_pairs_over_ranks():
+    p = random_problem(1500, len1=700, len2_range=(20, 600), seed=8)
+    assert plan.plan_pack(p, 4).mode == "tile"  # AUTO: too few items per GPU
+    blob = plan.plan_pack(p, 4, mode="stream")
+    assert blob.mode == "stream" and blob.header.world == 4
+    h, tab, items = blob.header, blob.seq_table(), blob.items()
+    pairs = blob.numpy()[h.off_pairs : h.off_pairs + 8 * h.npairs].view(np.dtype([("a", "<u4"), ("b", "<u4")]))
+    loads = []
+    for r in range(4):
+        sl = items[h.rank_first_item[r] : h.rank_first_item[r + 1]]
+        for pid in np.unique(sl["seq"]):
+            a, b = int(pairs["a"][pid]), int(pairs["b"][pid])
+            assert int(tab["home"][a]) == r and (b == 0xFFFFFFFF or int(tab["home"][b]) == r)
+        loads.append(int((tab["crow"][pairs["a"][sl["seq"]]].astype(np.int64) * 256).sum()))
+    assert max(loads) <= 1.05 * (sum(loads) / 4)
+    assert np.array_equal(plan.execute_blob_cpu(blob), solve_cpu(p, "fast"))
+    with pytest.raises(NativeError):
+        plan.plan_pack(p, 4, mode="pair")  # PAIR (CTA-per-pair) is single-GPU
