@@ -193,6 +193,7 @@ def run_ours(args):
         line["synthetic"] = synthetic_report(args)
     if m.get("fabric"):
         line["fabric"] = m["fabric"]
+        line["clocks_all_ranks"] = [{"sm_mhz": c.get("sm_mhz"), "reasons": c.get("reasons")} for c in m.get("clocks_all_ranks", [])]
     if m.get("large"):
         lg = m["large"]
         res_l = lg.pop("result")

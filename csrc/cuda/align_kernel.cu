@@ -58,13 +58,15 @@ struct KParams {
     uint32_t off_ctrl, off_key, off_cnt, off_out, off_blob;
     unsigned long long timeout_ns;
     uint32_t timeline;  // 1: record the globaltimer timeline in the control block
+    uint32_t skip_push; // 1: re-solve of the blob the peers already hold (debug / resident re-solve)
 };
 
 // Words of the control block at the start of every rank's symmetric buffer.
-constexpr uint32_t kCtlNext = 0, kCtlCtasDone = 1, kCtlRanksDone = 2, kCtlError = 3, kCtlFlags = 64;
+constexpr uint32_t kCtlNext = 0, kCtlCtasDone = 1, kCtlRanksDone = 2, kCtlError = 3, kCtlAllHere = 4, kCtlPushed = 5, kCtlFlags = 64;
 constexpr uint32_t kMaxChunks = SA_FABRIC_MAX_CHUNKS;
 // Optional timeline (globaltimer ns) in control words 16..31 as five 64-bit slots:
-// 0 earliest CTA start, 1 prefix ready (latest), 2 last item finished, 3 arrival sent, 4 all arrived.
+// 0 earliest CTA start, 1 prefix ready (latest), 2 last item finished, 3 arrival sent, 4 all arrived,
+// 5 first sight of the "whole blob is here" flag, 6 items that had to wait for chunk flags, 7 ns spent so.
 constexpr uint32_t kCtlTimes = 16;
 
 // ------------------------------------------------------------------ PTX helpers
@@ -197,6 +199,31 @@ __device__ __forceinline__ int first_k_on_diagonal(const int* lut_i, const unsig
 
 // Shared by every fabric launch: set when one of this CTA's bounded cross-GPU waits timed out.
 __shared__ uint32_t s_abort;
+// Set once this CTA has observed rank 0's "whole blob has landed" flag: no more per-item waits.
+__shared__ uint32_t s_all_here;
+
+// True when the caller may read the blob bytes [lo, hi) of a fabric launch on a rank other than 0.
+// Fast path: the cached / single "all here" flag. Slow path: the flags of the covering chunks.
+__device__ __forceinline__ bool fabric_bytes_ready(const KParams& p, const sa_blob_header* hdr, uint32_t* my_ctl,
+                                                   uint32_t lo, uint32_t hi) {
+    volatile uint32_t* const cached = &s_all_here;
+    if (*cached) return true;
+    unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
+    if ((int)(ld_acquire_sys(my_ctl + kCtlAllHere) - p.epoch) >= 0) {
+        *cached = 1u;
+        if (p.timeline) atomicMin(&times[5], global_ns());
+        return true;
+    }
+    const unsigned long long t0 = p.timeline ? global_ns() : 0ull;
+    const uint32_t cb = hdr->chunk_bytes;
+    for (uint32_t c = lo / cb; c <= (hi - 1u) / cb; ++c)
+        if (!wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns)) return false;
+    if (p.timeline) {
+        atomicAdd(&times[6], 1ull);
+        atomicAdd(&times[7], global_ns() - t0);
+    }
+    return true;
+}
 
 // Fabric prologue, once per CTA (requires a preceding __syncthreads after s_abort = 0):
 // rank 0 pushes its share of the blob's chunks to every peer and publishes their flags; the other
@@ -207,7 +234,9 @@ __device__ __forceinline__ void fabric_prologue(const KParams& p) {
     const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
     uint32_t* const my_ctl = reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl);
     if (kFabric && p.world > 1) {
-        if (p.rank == 0) {
+        if (p.rank == 0 && p.skip_push) {
+            // the peers still hold this blob from the previous launch (same epoch): nothing to send
+        } else if (p.rank == 0) {
             // ---- broadcast, fused with scoring: each CTA pushes its share of chunks, then scores
             const uint32_t total = hdr->total_bytes, chunk = hdr->chunk_bytes, nchunks = hdr->nchunks;
             for (uint32_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
@@ -232,6 +261,14 @@ __device__ __forceinline__ void fabric_prologue(const KParams& p) {
                     __threadfence_system();
                     for (uint32_t r = 1; r < p.world; ++r)
                         st_relaxed_sys(reinterpret_cast<uint32_t*>(p.peer[r] + p.off_ctrl) + kCtlFlags + c, p.epoch);
+                    // The CTA that publishes the last chunk also raises one "everything is here" flag, so
+                    // that peers stop polling (and stop invalidating their L1) per item once the broadcast
+                    // is over. Every pusher fenced at system scope before it counted itself.
+                    if (atomicAdd(&my_ctl[kCtlPushed], 1u) + 1u == nchunks) {
+                        my_ctl[kCtlPushed] = 0u;
+                        for (uint32_t r = 1; r < p.world; ++r)
+                            st_relaxed_sys(reinterpret_cast<uint32_t*>(p.peer[r] + p.off_ctrl) + kCtlAllHere, p.epoch);
+                    }
                 }
             }
         } else {
@@ -321,13 +358,13 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
     uint32_t parity = 0;
     uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
     unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
-    const bool timeline = kFabric && p.timeline != 0u;
+    const bool timeline = kFabric && p.timeline != 0u && !prologue_done;
     if (timeline && tid == 0) atomicMin(&times[0], global_ns());
 
     if (tid == 0) {
         mbar_init(bar, 1);
         mbar_fence_init();
-        if (!prologue_done) s_abort = 0u;
+        if (!prologue_done) s_abort = 0u, s_all_here = 0u;
     }
     __syncthreads();
 
@@ -364,9 +401,7 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
             if (kFabric && p.rank != 0 && it < item_end) {  // this sequence's letters may still be in flight
                 const sa_seq_desc d = seqtab[items[it].seq];
                 const uint32_t bytes = ((uint32_t)d.crow * ((uint32_t)kWarps >> d.wd_log2) + 15u) & ~15u;
-                const uint32_t c0 = d.off / hdr->chunk_bytes, c1 = (d.off + bytes - 1u) / hdr->chunk_bytes;
-                bool ok = true;
-                for (uint32_t c = c0; ok && c <= c1; ++c) ok = wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns);
+                const bool ok = fabric_bytes_ready(p, hdr, my_ctl, d.off, d.off + bytes);
                 if (!ok) {
                     s_abort = 1u;
                     atomicExch(my_ctl + kCtlError, 1u);
@@ -492,7 +527,7 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
         if (ctl[1]) {
             if (tid == 0) {
                 if (kFabric) {
-                    __threadfence_system();
+                    if (sd.home == p.rank) __threadfence(); else __threadfence_system();
                     red[0] = atomicMax_system(keyp, 0ull);  // coherent read of the final key
                 } else {
                     __threadfence();
@@ -828,6 +863,13 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
         if (lane == 0) item = item_begin + atomicAdd(&my_ctl[kCtlNext], 1u);
         item = __shfl_sync(0xFFFFFFFFu, item, 0);
         if (item >= item_end || (kFabric && *reinterpret_cast<volatile uint32_t*>(&s_abort) != 0u)) break;
+        if (kFabric && p.timeline && lane == 0) {  // when were 25 / 50 / 75 % of this rank's items handed out?
+            const uint32_t n_it = item_end - item_begin, k = item - item_begin;
+            unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
+            if (k == n_it / 4) times[8] = global_ns();
+            if (k == n_it / 2) times[9] = global_ns();
+            if (k == (n_it / 4) * 3) times[10] = global_ns();
+        }
         const uint32_t pid = items[item].seq, tile = items[item].tile;
         const uint32_t ia = pairs[pid].seq, ib = pairs[pid].tile;
         const bool has_b = ib != SA_NO_SEQ;
@@ -843,10 +885,8 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
         if (kFabric && p.rank != 0) {  // the two sequences' letters may still be in flight from rank 0
             uint32_t ok = 1u;
             if (lane == 0) {
-                const uint32_t cb = hdr->chunk_bytes;
-                for (uint32_t c = da.off / cb; ok && c <= (da.off + rows - 1u) / cb; ++c) ok = wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns);
-                if (has_b)
-                    for (uint32_t c = db.off / cb; ok && c <= (db.off + rows - 1u) / cb; ++c) ok = wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns);
+                ok = fabric_bytes_ready(p, hdr, my_ctl, da.off, da.off + rows) ? 1u : 0u;
+                if (ok && has_b) ok = fabric_bytes_ready(p, hdr, my_ctl, db.off, db.off + rows) ? 1u : 0u;
                 if (!ok) {
                     *reinterpret_cast<volatile uint32_t*>(&s_abort) = 1u;
                     atomicExch(my_ctl + kCtlError, 1u);
@@ -961,7 +1001,7 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
                 unsigned long long fk = 0ull;
                 if (lane == 0) {
                     if (kFabric) {
-                        __threadfence_system();
+                        if (da.home == p.rank) __threadfence(); else __threadfence_system();
                         fk = atomicMax_system(kp, 0ull);
                     } else {
                         __threadfence();
@@ -989,10 +1029,16 @@ __global__ void __launch_bounds__(kThreads, 2) sa_score_stream_kernel(const KPar
 // One fabric kernel for both modes: ranks other than 0 launch before they know anything about
 // the problem, so the mode is read from the blob header once the broadcast prefix has landed.
 __global__ void __launch_bounds__(kThreads, 2) sa_score_fabric_kernel(const KParams p) {
-    if (threadIdx.x == 0) s_abort = 0u;
+    unsigned long long* const times = reinterpret_cast<unsigned long long*>(reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) + kCtlTimes);
+    if (threadIdx.x == 0) {
+        s_abort = 0u;
+        s_all_here = 0u;
+        if (p.timeline) atomicMin(&times[0], global_ns());
+    }
     __syncthreads();
     fabric_prologue(p);
     __syncthreads();
+    if (p.timeline && threadIdx.x == 0) atomicMax(&times[1], global_ns());
     const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
     if (s_abort == 0u && (hdr->flags & SA_FLAG_STREAM_MODE))
         stream_body<true>(p, true);
@@ -1462,6 +1508,7 @@ int sa_cuda_fabric_solve(const sa_fabric_desc* f, const sa_blob_header* header, 
     p.off_blob = f->layout.off_blob;
     p.timeout_ns = (unsigned long long)(f->timeout_ms ? f->timeout_ms : 10000u) * 1000000ull;
     p.timeline = f->pad0 & 1u;
+    p.skip_push = (f->pad0 >> 1) & 1u;
     p.blob = p.peer[f->rank] + p.off_blob;
     p.write_empty = f->rank == 0 ? 1u : 0u;
     // Ranks other than 0 know nothing about the problem at launch time, so every rank launches the

@@ -311,7 +311,9 @@ typedef struct sa_fabric_desc {
     uint32_t epoch;         /* 1, 2, 3, ... — the same on every rank for the same solve      */
     uint32_t use_multicast; /* broadcast with multimem.st through mc_base (else P2P stores)  */
     uint32_t timeout_ms;    /* bound on every cross-GPU wait (0 = 10 s)                       */
-    uint32_t pad0;          /* bit 0: record a globaltimer timeline in control words 16..31 (debug) */
+    uint32_t pad0;          /* bit 0: record a globaltimer timeline in control words 16..31 (debug);
+                               bit 1: re-solve the blob of the previous launch without re-broadcasting it
+                               (pass the previous epoch again) */
     void* peer_base[SA_MAX_WORLD]; /* rank r's symmetric buffer as mapped in THIS process     */
     void* mc_base;                 /* multicast mapping of the buffer, or NULL                */
     sa_fabric_layout_t layout;

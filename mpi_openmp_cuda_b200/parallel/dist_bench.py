@@ -6,6 +6,8 @@ scoring + gather; the max over ranks is still taken, as the contract asks.
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -126,6 +128,8 @@ def time_ours_distributed(problem, steps: int, warmup: int, large_problem=None):
     e2e_ms = [e2e_step(False) for _ in range(steps)]
     pre_ms = [e2e_step(True) for _ in range(steps)]
     clocks = sampler.stop()
+    all_clocks = [None] * world
+    dist.all_gather_object(all_clocks, clocks)
     solver.check()
     # ---- optional: the same fabric path with milliseconds of work per GPU (fixed costs amortised)
     large = None
@@ -135,6 +139,7 @@ def time_ours_distributed(problem, steps: int, warmup: int, large_problem=None):
         lres = solver.fetch(int(need[2].item()))
         lres = lres.copy() if rank == 0 else None
         lms = []
+        lsampler = ClockSampler(local).start()
         for _ in range(max(3, min(steps, 10)) + 2):
             torch.cuda.synchronize()
             dist.barrier()
@@ -142,15 +147,30 @@ def time_ours_distributed(problem, steps: int, warmup: int, large_problem=None):
             flusher.flush()
             align()
             e0.record()
-            fabric.launch(lblob.header if rank == 0 else None)
+            fabric.launch(lblob.header if rank == 0 else None, resident=os.environ.get("SA_BENCH_RESIDENT") == "1")
             e1.record()
             e1.synchronize()
             lms.append(e0.elapsed_time(e1))
+        lclocks = [None] * world
+        dist.all_gather_object(lclocks, lsampler.stop())
+        own_ms = [round(x, 4) for x in lms[2:]]
+        per_rank_ms = [None] * world
+        dist.all_gather_object(per_rank_ms, sum(own_ms) / len(own_ms))
         lms = _max_over_ranks(lms[2:])
         solver.check()
+        if fabric.timeline:
+            import sys
+
+            tl = [None] * world
+            dist.all_gather_object(tl, fabric.read_timeline())
+            if rank == 0:
+                print("fabric timeline, large config (us since each rank's first CTA; last step):", tl, file=sys.stderr)
         if rank == 0:
             large = {"nseq": large_problem.nseq, "candidates": large_problem.candidates(), "kernel_ms": sum(lms) / len(lms),
-                     "kernel_ms_min": min(lms), "result": lres, "h2d_bytes": lblob.nbytes}
+                     "kernel_ms_min": min(lms), "result": lres, "h2d_bytes": lblob.nbytes,
+                     "kernel_ms_per_rank": per_rank_ms,
+                     "clocks_per_rank": [{"sm_mhz": c.get("sm_mhz"), "sm_mhz_min": c.get("sm_mhz_min"), "power_w_max": c.get("power_w_max"),
+                                          "reasons": c.get("reasons")} for c in lclocks]}
         # put the headline problem back into rank 0's buffer for the final consistency check
         solver.launch_packed(blob)
         solver.fetch(nseq)
@@ -165,7 +185,7 @@ def time_ours_distributed(problem, steps: int, warmup: int, large_problem=None):
     assert np.array_equal(final, res), "results changed between steps"
     out = {
         "kernel_ms": kernel_ms, "e2e_ms": e2e_ms, "e2e_prepacked_ms": pre_ms, "launches": int(total_launches.item()),
-        "clocks": clocks, "h2d": blob.nbytes, "d2h": nseq * 16, "result": res,
+        "clocks": clocks, "clocks_all_ranks": all_clocks, "h2d": blob.nbytes, "d2h": nseq * 16, "result": res,
         "padded_cells": int(blob.header.padded_cells), "nitems": blob.nitems,
         "fabric": {"multicast": fabric.use_multicast, "world": world},
         "large": large,

@@ -107,9 +107,14 @@ class Fabric:
 
     def read_timeline(self) -> dict:
         """After a synchronised launch with SA_FABRIC_TIMELINE=1: microseconds since this rank's first CTA started."""
-        t = self.buf[self.layout.off_ctrl + 64 : self.layout.off_ctrl + 104].view(torch.int64).cpu().tolist()
-        names = ["start", "prefix_ready", "items_done", "arrival_sent", "all_arrived"]
-        return {n: (None if v in (0,) else (v - t[0]) / 1e3) for n, v in zip(names, t)} | {"start_abs_ns": t[0]}
+        t = self.buf[self.layout.off_ctrl + 64 : self.layout.off_ctrl + 64 + 88].view(torch.int64).cpu().tolist()
+        names = ["start", "prefix_ready", "items_done", "arrival_sent", "all_arrived", "all_here_seen"]
+        big = torch.iinfo(torch.int64).max
+        out = {n: (None if v in (0, big) else round((v - t[0]) / 1e3, 2)) for n, v in zip(names, t)}
+        out["items_that_waited"] = t[6]
+        out["wait_us_total"] = round(t[7] / 1e3, 1)
+        out["quartiles_handed_out"] = [None if v == 0 else round((v - t[0]) / 1e3, 1) for v in t[8:11]]
+        return out
 
     # -- the two primitives in isolation (benchmarks/fabric_sweep.py)
     def bcast(self, nbytes: int, ctas: int = 0) -> None:
@@ -129,15 +134,20 @@ class Fabric:
         N.check(self.lib.sa_cuda_fabric_argmax(C.byref(self._desc), C.c_void_p(keys.data_ptr()), int(keys.numel()),
                                                int(ctas), C.c_void_p(stream)))
 
-    def launch(self, header: N.BlobHeader | None) -> None:
-        """Enqueue this rank's kernel of the next solve on the current stream."""
-        self.epoch += 1
+    def launch(self, header: N.BlobHeader | None, resident: bool = False) -> None:
+        """Enqueue this rank's kernel of the next solve on the current stream.
+        resident=True re-solves the blob every rank already holds from the previous launch
+        (no broadcast; every rank must pass the same value)."""
+        if not resident:
+            self.epoch += 1
         d = self._desc
         d.epoch = self.epoch
+        d.pad0 = (1 if self.timeline else 0) | (2 if resident else 0)
         if self.timeline:  # slot 0 is a running minimum: re-arm it (and the maxima) before every launch
-            t = self.buf[self.layout.off_ctrl + 64 : self.layout.off_ctrl + 128].view(torch.int64)
+            t = self.buf[self.layout.off_ctrl + 64 : self.layout.off_ctrl + 64 + 88].view(torch.int64)
             t.zero_()
             t[0] = torch.iinfo(torch.int64).max
+            t[5] = torch.iinfo(torch.int64).max
         stream = torch.cuda.current_stream(self.device).cuda_stream
         hdr = C.byref(header) if header is not None else None
         with torch.cuda.device(self.device):
