@@ -244,6 +244,7 @@ def run_reference(args):
 
 if __name__ == "__main__":
     a = parse_args()
+    a.warmup = max(a.warmup, 3)  # timing rule: at least three untimed warm-up steps
     # exactly ONE line on stdout: keep library banners (e.g. "NCCL version ...") off fd 1
     sys.stdout.flush()
     _real = os.dup(1)
