@@ -51,6 +51,7 @@ struct KParams {
     uint32_t item_begin, item_end;
     uint32_t s2_cap, win_cap;   // shared-memory capacities (bytes, multiples of 16)
     uint32_t write_empty;       // 1: this launch writes the rows of candidate-free sequences
+    uint32_t h_off_lut, h_off_seq1, h_off_seqtab, h_off_items, h_nseq;  // header fields the host already knows (non-fabric)
     // ---- fabric (multi-GPU) launches only; see sa_cuda_fabric_solve
     uint32_t rank, world, epoch, use_mc;
     unsigned char* peer[SA_MAX_WORLD];  // every rank's symmetric buffer as mapped into this process
@@ -353,7 +354,6 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
-    if (!kFabric && hdr->magic != SA_BLOB_MAGIC) return;  // never walk memory that is not a packed problem
     const uint32_t bar = smem_u32(mbar);
     uint32_t parity = 0;
     uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
@@ -372,9 +372,16 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
     const bool dead_on_arrival = kFabric && s_abort != 0u;
     if (timeline && tid == 0) atomicMax(&times[1], global_ns());
 
-    const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + (dead_on_arrival ? 0u : hdr->off_seqtab));
-    const sa_item* const items = reinterpret_cast<const sa_item*>(p.blob + (dead_on_arrival ? 0u : hdr->off_items));
-    const unsigned char* const seq1g = p.blob + (dead_on_arrival ? 0u : hdr->off_seq1);
+    // A single-GPU launch gets the header's offsets as kernel parameters (the host has the header):
+    // no dependent read of cold global memory before the first item can be fetched.
+    const uint32_t off_seqtab = kFabric ? (dead_on_arrival ? 0u : hdr->off_seqtab) : p.h_off_seqtab;
+    const uint32_t off_items = kFabric ? (dead_on_arrival ? 0u : hdr->off_items) : p.h_off_items;
+    const uint32_t off_seq1 = kFabric ? (dead_on_arrival ? 0u : hdr->off_seq1) : p.h_off_seq1;
+    const uint32_t off_lut = kFabric ? (dead_on_arrival ? 0u : hdr->off_lut) : p.h_off_lut;
+    const uint32_t nseq_all = kFabric ? (dead_on_arrival ? 0u : hdr->nseq) : p.h_nseq;
+    const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + off_seqtab);
+    const sa_item* const items = reinterpret_cast<const sa_item*>(p.blob + off_items);
+    const unsigned char* const seq1g = p.blob + off_seq1;
     const uint32_t item_begin = kFabric ? (dead_on_arrival ? 0u : hdr->rank_first_item[p.rank]) : p.item_begin;
     const uint32_t item_end = kFabric ? (dead_on_arrival ? 0u : hdr->rank_first_item[p.rank + 1]) : p.item_end;
     int4* const out = kFabric ? reinterpret_cast<int4*>(p.peer[0] + p.off_out) : p.out;
@@ -382,22 +389,15 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
     // Sequences longer than Seq1 have no candidates: (INT_MIN, 0, 0) as the reference's
     // untouched `max` (cudaFunctions.cu:113,170-172).
     if (p.write_empty && !dead_on_arrival) {
-        for (uint32_t s = blockIdx.x * kThreads + tid; s < hdr->nseq; s += gridDim.x * kThreads)
+        for (uint32_t s = blockIdx.x * kThreads + tid; s < nseq_all; s += gridDim.x * kThreads)
             if (seqtab[s].ntiles == 0) out[s] = make_int4(INT_MIN, 0, 0, 0);
     }
-    // Pair-value table -> shared memory, once per CTA.
-    if (!dead_on_arrival) {
-        if (tid == 0) {
-            mbar_expect_tx(bar, kLutBytes);
-            bulk_g2s(smem_u32(lut_b), p.blob + hdr->off_lut, kLutBytes, bar);
-        }
-        mbar_wait(bar, parity);
-        parity ^= 1u;
-    }
 
+    bool first = true;  // CTA-uniform: the first item is blockIdx.x (no queue round trip) and brings the table along
     for (;;) {
         if (tid == 0) {
-            const uint32_t it = item_begin + atomicAdd(&my_ctl[kCtlNext], 1u);
+            uint32_t it = item_begin + (first ? blockIdx.x : gridDim.x + atomicAdd(&my_ctl[kCtlNext], 1u));
+            if (!kFabric && first && hdr->magic != SA_BLOB_MAGIC) it = 0xFFFFFFFFu;  // never walk memory that is not a packed problem
             if (kFabric && p.rank != 0 && it < item_end) {  // this sequence's letters may still be in flight
                 const sa_seq_desc d = seqtab[items[it].seq];
                 const uint32_t bytes = ((uint32_t)d.crow * ((uint32_t)kWarps >> d.wd_log2) + 15u) & ~15u;
@@ -427,12 +427,14 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
         if (tid == 0) {
             const uint32_t s2_bytes = (rows_padded + 15u) & ~15u;
             const uint32_t win_bytes = (rows_padded + tn + 15u) & ~15u;
-            mbar_expect_tx(bar, s2_bytes + win_bytes);
+            mbar_expect_tx(bar, s2_bytes + win_bytes + (first ? kLutBytes : 0u));
+            if (first) bulk_g2s(smem_u32(lut_b), p.blob + off_lut, kLutBytes, bar);  // pair-value table, once per CTA
             bulk_g2s(smem_u32(s2), p.blob + sd.off, s2_bytes, bar);
             bulk_g2s(smem_u32(win), seq1g + n0, win_bytes, bar);
         }
         mbar_wait(bar, parity);
         parity ^= 1u;
+        first = false;
 
         // ---- scan: this warp = offset group g, row chunk q
         {
@@ -505,7 +507,11 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
             unsigned long long v = lane < (uint32_t)kWarps ? red[lane] : 0ull;
 #pragma unroll
             for (int o = 8; o > 0; o >>= 1) v = umax64(v, __shfl_xor_sync(0xFFFFFFFFu, v, o));
-            if (lane == 0) {
+            if (lane == 0 && sd.ntiles == 1) {  // the sequence's only tile: nothing to combine, no atomics
+                red[0] = v;
+                ctl[1] = 1u;
+                ctl[2] = 0x7FFFFFFFu;
+            } else if (lane == 0) {
                 unsigned int old;
                 if (kFabric) {
                     atomicMax_system(keyp, v);
@@ -525,7 +531,7 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
 
         // ---- last tile of this sequence: find the first k on the winning diagonal
         if (ctl[1]) {
-            if (tid == 0) {
+            if (tid == 0 && sd.ntiles != 1) {
                 if (kFabric) {
                     if (sd.home == p.rank) __threadfence(); else __threadfence_system();
                     red[0] = atomicMax_system(keyp, 0ull);  // coherent read of the final key
@@ -542,8 +548,10 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
                                                                       sd.len, bestv, scan, csum, &ctl[2]);
             if (tid == 0) {
                 out[seq] = make_int4(bestv, (int)nwin, kres, 0);
-                *keyp = 0ull;  // leave the scratch zeroed for the next launch
-                *cntp = 0u;
+                if (sd.ntiles != 1) {
+                    *keyp = 0ull;  // leave the scratch zeroed for the next launch
+                    *cntp = 0u;
+                }
             }
         }
     }
@@ -1136,6 +1144,11 @@ int sa_cuda_solve_blob(const void* d_blob, const sa_blob_header* h, int32_t* d_o
     p.ctrl = reinterpret_cast<unsigned int*>(sc + key_bytes(h->nseq) + cnt_bytes(h->nseq));
     p.item_begin = 0;
     p.item_end = h->nitems;
+    p.h_off_lut = h->off_lut;
+    p.h_off_seq1 = h->off_seq1;
+    p.h_off_seqtab = h->off_seqtab;
+    p.h_off_items = h->off_items;
+    p.h_nseq = h->nseq;
     p.s2_cap = (h->max_rows_padded + 15u) & ~15u;
     p.win_cap = (h->max_window_bytes + 15u) & ~15u;
     p.write_empty = 1;
