@@ -6,7 +6,6 @@ from __future__ import annotations
 
 import os
 from functools import lru_cache
-from pathlib import Path
 
 from ..utils import build as _build
 

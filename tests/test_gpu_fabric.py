@@ -74,3 +74,38 @@ def test_two_gpus_stream_mode_through_the_fabric():
                          capture_output=True, cwd=ROOT, timeout=600, env=dict(os.environ, PYTHONPATH=str(ROOT)))
     assert out.returncode == 0, out.stderr.decode()[-3000:]
     assert b"stream fabric ok" in out.stdout
+
+
+def test_dead_peer_times_out_instead_of_hanging():
+    """Fault injection for SURVEY.md 5.3 / R11: a rank whose peer never broadcasts must come back with
+    an error word, not spin forever (the reference's exit(1) leaves its peers inside MPI collectives).
+    Needs one GPU only: 'rank 1' is launched alone, with two local buffers standing in for the two
+    ranks' symmetric buffers; nobody ever plays rank 0."""
+    import ctypes as C
+
+    import torch
+
+    from mpi_openmp_cuda_b200.ops import _native as N
+    from mpi_openmp_cuda_b200.parallel.fabric import FabricDesc, FabricLayout
+
+    lib = N.cuda()
+    lib.sa_fabric_layout.argtypes = [C.c_uint32, C.c_size_t, C.POINTER(FabricLayout)]
+    lib.sa_cuda_fabric_solve.argtypes = [C.POINTER(FabricDesc), C.POINTER(N.BlobHeader), C.c_void_p]
+    lay = FabricLayout()
+    N.check(lib.sa_fabric_layout(64, 1 << 20, C.byref(lay)))
+    bufs = [torch.zeros(int(lay.total_bytes), dtype=torch.uint8, device="cuda:0") for _ in range(2)]
+    d = FabricDesc()
+    d.rank, d.world, d.epoch, d.use_multicast, d.timeout_ms = 1, 2, 1, 0, 50
+    d.peer_base[0], d.peer_base[1] = bufs[0].data_ptr(), bufs[1].data_ptr()
+    d.layout = lay
+    t0 = torch.cuda.Event(enable_timing=True)
+    t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    N.check(lib.sa_cuda_fabric_solve(C.byref(d), None, None))
+    t1.record()
+    torch.cuda.synchronize()
+    err = int(bufs[1][lay.off_ctrl + 12 : lay.off_ctrl + 16].view(torch.int32).item())
+    assert err == 1, "the waiting rank must report the timeout"
+    assert 40.0 < t0.elapsed_time(t1) < 2000.0  # bounded by timeout_ms, not by luck
+    # it still told 'rank 0' that it is done, so a live rank 0 would not wait for it forever
+    assert int(bufs[0][lay.off_ctrl + 8 : lay.off_ctrl + 12].view(torch.int32).item()) == 1
