@@ -48,3 +48,17 @@ def test_gpu_mode_is_byte_identical(final_bin, shipped_inputs, i):
     path, gold = shipped_inputs[i]
     out = subprocess.run([str(final_bin)], stdin=open(path, "rb"), capture_output=True, check=True)
     assert out.stdout == gold.read_bytes()
+
+
+@pytest.mark.gpu
+def test_gpu_mode_across_two_gpus_is_byte_identical(final_bin, shipped_inputs):
+    """`./final --gpus 2` = the reference's `mpiexec -np 2 ./final` (makefile:11): same bytes on stdout."""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    for i in (1, 3):
+        path, gold = shipped_inputs[i]
+        out = subprocess.run([str(final_bin), "--gpus", "2"], stdin=open(path, "rb"), capture_output=True, timeout=600)
+        assert out.returncode == 0, out.stderr.decode()[-2000:]
+        assert out.stdout == gold.read_bytes()
