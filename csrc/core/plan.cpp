@@ -16,6 +16,7 @@
 // so per offset n the best k is a running max of the prefix difference of two neighbouring
 // diagonals — O(len1*len2) instead of the reference's O(len1*len2^2).
 #include <algorithm>
+#include <atomic>
 #include <climits>
 #include <cstdlib>
 #include <cstring>
@@ -124,11 +125,10 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     }
     int64_t maxw = 0;
     for (int i = 0; i < 4; ++i) maxw = std::max<int64_t>(maxw, std::llabs((int64_t)p->weights[i]));
-    const Alphabet al = build_alphabet(*p);
-    if (!al.ok) {
-        set_error("more than five distinct non-letter bytes in the input");
-        return SA_ERR_UNSUPPORTED;
-    }
+    // Optimistic alphabet: inputs are almost always pure letters, so the letters are coded without
+    // looking at the data; the first non-letter byte met while filling triggers one full scan
+    // (build_alphabet) and a refill. Saves a pass over every byte on the latency-critical path.
+    Alphabet al = letters_only_alphabet();
     uint32_t max_len2 = 0, nvalid = 0;
     for (uint32_t s = 0; s < nseq; ++s) {
         const size_t l2 = p->seq2[s].size();
@@ -424,10 +424,21 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     h->world = (uint32_t)world;
     h->value_min = (int32_t)wmin;
     h->value_range = (uint32_t)wrange;
-    build_lut(al, p->weights, reinterpret_cast<int32_t*>(base + off_lut));
-    for (uint32_t j = 0; j < len1; ++j) base[off_seq1 + j] = (unsigned char)(al.code[(unsigned char)p->seq1[j]] * 4);
     sa_seq_desc* tab = reinterpret_cast<sa_seq_desc*>(base + off_seqtab);
+    for (int attempt = 0; attempt < 2; ++attempt) {
+    std::atomic<int> unknown_byte{0};
+    build_lut(al, p->weights, reinterpret_cast<int32_t*>(base + off_lut));
+    {
+        int bad = 0;
+        for (uint32_t j = 0; j < len1; ++j) {
+            const int c = al.code[(unsigned char)p->seq1[j]];
+            bad |= c;
+            base[off_seq1 + j] = (unsigned char)(c * 4);
+        }
+        if (bad < 0) unknown_byte.store(1);
+    }
     parallel_for(nseq, total, [&](uint32_t s0, uint32_t s1) {
+        int bad = 0;
         for (uint32_t s = s0; s < s1; ++s) {
             const SeqPlan& sp = plans[s];
             tab[s].off = seq_off[s];
@@ -439,11 +450,24 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
             tab[s].crow = (uint16_t)sp.crow;
             const std::string& q = p->seq2[s];
             unsigned char* dstq = base + seq_off[s];
-            for (size_t i = 0; i < q.size(); ++i) dstq[i] = (unsigned char)al.code[(unsigned char)q[i]];
+            for (size_t i = 0; i < q.size(); ++i) {
+                const int c = al.code[(unsigned char)q[i]];
+                bad |= c;
+                dstq[i] = (unsigned char)c;
+            }
             const size_t slot = (s + 1 < nseq ? seq_off[s + 1] : total) - seq_off[s];
             std::memset(dstq + q.size(), 0, slot - q.size());
         }
+        if (bad < 0) unknown_byte.store(1);
     });
+    if (!unknown_byte.load()) break;
+    // a byte outside A-Z: assign the spare codes from a full scan and fill once more
+    al = build_alphabet(*p);
+    if (!al.ok || attempt == 1) {
+        set_error("more than five distinct non-letter bytes in the input");
+        return SA_ERR_UNSUPPORTED;
+    }
+    }
     sa_item* items = reinterpret_cast<sa_item*>(base + off_items);
     uint32_t w = 0;
     for (int r = 0; r < world; ++r) {

@@ -98,6 +98,17 @@ const Groups& groups() {
 
 }  // namespace
 
+Alphabet letters_only_alphabet() {
+    Alphabet al;
+    for (int i = 0; i < 256; ++i) al.code[i] = -2;  // any non-letter byte is "unknown" (negative)
+    std::memset(al.byte_of, 0, sizeof(al.byte_of));
+    for (int c = 0; c < 26; ++c) {
+        al.code['A' + c] = (int16_t)(1 + c);
+        al.byte_of[1 + c] = (unsigned char)('A' + c);
+    }
+    return al;
+}
+
 Alphabet build_alphabet(const sa_problem& p) {
     Alphabet al;
     for (int i = 0; i < 256; ++i) al.code[i] = -2;  // -2 = does not occur
