@@ -17,7 +17,7 @@ CUDA_SRC := csrc/cuda/align_kernel.cu csrc/cuda/fabric_bench.cu
 CORE_LIB := $(LIBDIR)/libseqalign_core.so
 CUDA_LIB := $(LIBDIR)/libseqalign_cuda.so
 
-.PHONY: build core cuda clean run runOn2 test sass
+.PHONY: build core cuda clean run runOn2 test sass asan tsan
 
 build: core cuda final
 
@@ -53,3 +53,17 @@ test: build
 
 sass: cuda
 	$(CUDA_HOME)/bin/cuobjdump -sass $(CUDA_LIB) > profiles/align_kernel.sass
+
+# Host-side sanitizer runs: the whole core library + tests/native/core_selftest.cpp
+# under ASan+UBSan, and under TSan for the multi-threaded packer and oracle.
+SAN_CXX ?= $(shell test -x /usr/bin/g++ && echo /usr/bin/g++ || echo $(CXX))  # a compiler that ships the sanitizer runtimes
+SELFTEST_INPUTS := data/input1.txt data/input2.txt data/input5.txt data/input6.txt data/input4.txt
+asan:
+	@mkdir -p build
+	$(SAN_CXX) -O1 -g -std=c++17 -Iinclude -pthread -fsanitize=address,undefined -fno-omit-frame-pointer -fno-sanitize-recover=undefined \
+	    -o build/core_selftest_asan tests/native/core_selftest.cpp $(CORE_SRC)
+	ASAN_OPTIONS=detect_leaks=1 build/core_selftest_asan $(SELFTEST_INPUTS)
+tsan:
+	@mkdir -p build
+	$(SAN_CXX) -O1 -g -std=c++17 -Iinclude -pthread -fsanitize=thread -o build/core_selftest_tsan tests/native/core_selftest.cpp $(CORE_SRC)
+	build/core_selftest_tsan data/input1.txt data/input6.txt

@@ -205,6 +205,13 @@ int sa_parse(const char* text, size_t len, sa_problem** out) {
         delete p;
         return SA_ERR_PARSE;
     }
+    // every sequence needs at least one byte and one separator: a count larger than that can allow is
+    // a malformed input, and must not be allowed to size an allocation (found by `make asan`)
+    if ((size_t)n > (size_t)(cur.end - cur.p + 1) / 2 + 1) {
+        sa::set_error("parse error: expected " + std::to_string(n) + " sequences, the input is too short to hold them");
+        delete p;
+        return SA_ERR_PARSE;
+    }
     p->seq2.resize((size_t)n);
     for (int32_t i = 0; i < n; ++i) {
         if (!cur.read_token(&p->seq2[(size_t)i])) {
