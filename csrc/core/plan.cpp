@@ -426,47 +426,47 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     h->value_range = (uint32_t)wrange;
     sa_seq_desc* tab = reinterpret_cast<sa_seq_desc*>(base + off_seqtab);
     for (int attempt = 0; attempt < 2; ++attempt) {
-    std::atomic<int> unknown_byte{0};
-    build_lut(al, p->weights, reinterpret_cast<int32_t*>(base + off_lut));
-    {
-        int bad = 0;
-        for (uint32_t j = 0; j < len1; ++j) {
-            const int c = al.code[(unsigned char)p->seq1[j]];
-            bad |= c;
-            base[off_seq1 + j] = (unsigned char)(c * 4);
-        }
-        if (bad < 0) unknown_byte.store(1);
-    }
-    parallel_for(nseq, total, [&](uint32_t s0, uint32_t s1) {
-        int bad = 0;
-        for (uint32_t s = s0; s < s1; ++s) {
-            const SeqPlan& sp = plans[s];
-            tab[s].off = seq_off[s];
-            tab[s].len = (uint16_t)sp.len;
-            tab[s].ndiag = sp.ndiag;
-            tab[s].ntiles = (uint16_t)sp.ntiles;
-            tab[s].wd_log2 = (uint8_t)sp.wd_log2;
-            tab[s].home = home[s];
-            tab[s].crow = (uint16_t)sp.crow;
-            const std::string& q = p->seq2[s];
-            unsigned char* dstq = base + seq_off[s];
-            for (size_t i = 0; i < q.size(); ++i) {
-                const int c = al.code[(unsigned char)q[i]];
+        std::atomic<int> unknown_byte{0};
+        build_lut(al, p->weights, reinterpret_cast<int32_t*>(base + off_lut));
+        {
+            int bad = 0;
+            for (uint32_t j = 0; j < len1; ++j) {
+                const int c = al.code[(unsigned char)p->seq1[j]];
                 bad |= c;
-                dstq[i] = (unsigned char)c;
+                base[off_seq1 + j] = (unsigned char)(c * 4);
             }
-            const size_t slot = (s + 1 < nseq ? seq_off[s + 1] : total) - seq_off[s];
-            std::memset(dstq + q.size(), 0, slot - q.size());
+            if (bad < 0) unknown_byte.store(1);
         }
-        if (bad < 0) unknown_byte.store(1);
-    });
-    if (!unknown_byte.load()) break;
-    // a byte outside A-Z: assign the spare codes from a full scan and fill once more
-    al = build_alphabet(*p);
-    if (!al.ok || attempt == 1) {
-        set_error("more than five distinct non-letter bytes in the input");
-        return SA_ERR_UNSUPPORTED;
-    }
+        parallel_for(nseq, total, [&](uint32_t s0, uint32_t s1) {
+            int bad = 0;
+            for (uint32_t s = s0; s < s1; ++s) {
+                const SeqPlan& sp = plans[s];
+                tab[s].off = seq_off[s];
+                tab[s].len = (uint16_t)sp.len;
+                tab[s].ndiag = sp.ndiag;
+                tab[s].ntiles = (uint16_t)sp.ntiles;
+                tab[s].wd_log2 = (uint8_t)sp.wd_log2;
+                tab[s].home = home[s];
+                tab[s].crow = (uint16_t)sp.crow;
+                const std::string& q = p->seq2[s];
+                unsigned char* dstq = base + seq_off[s];
+                for (size_t i = 0; i < q.size(); ++i) {
+                    const int c = al.code[(unsigned char)q[i]];
+                    bad |= c;
+                    dstq[i] = (unsigned char)c;
+                }
+                const size_t slot = (s + 1 < nseq ? seq_off[s + 1] : total) - seq_off[s];
+                std::memset(dstq + q.size(), 0, slot - q.size());
+            }
+            if (bad < 0) unknown_byte.store(1);
+        });
+        if (!unknown_byte.load()) break;
+        // a byte outside A-Z: assign the spare codes from a full scan and fill once more
+        al = build_alphabet(*p);
+        if (!al.ok || attempt == 1) {
+            set_error("more than five distinct non-letter bytes in the input");
+            return SA_ERR_UNSUPPORTED;
+        }
     }
     sa_item* items = reinterpret_cast<sa_item*>(base + off_items);
     uint32_t w = 0;

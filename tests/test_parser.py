@@ -58,3 +58,9 @@ def test_serialize_roundtrip():
     p = Problem.from_parts((4, 3, 2, 10), "abcXYZ", ["ab", "XyZ"])
     q = Problem.parse(p.serialize())
     assert q.weights == p.weights and q.seq1 == b"ABCXYZ" and q.seq2(1) == b"XYZ"
+
+
+def test_hostile_sequence_count_is_a_parse_error_not_an_allocation():
+    # found by `make asan`: the count must not size an allocation before the tokens are seen
+    with pytest.raises(NativeError):
+        Problem.parse(b"1 1 1 1 A 2147483647 A")
