@@ -79,7 +79,7 @@ def bench_reference(args, rank: int, world: int):
     cands = problem.candidates()
     data = problem.serialize() if args.scale * n_gpus > 1 else (ROOT / "data" / args.input).read_bytes()
     variant = os.environ.get("REF_VARIANT", "final")
-    budget_s = float(os.environ.get("REF_BUDGET_S", "600"))
+    budget_s = float(os.environ.get("REF_BUDGET_S", "300"))
     floor_input = (ROOT / "data" / "input5.txt").read_bytes()
     try:
         t_first, rc, out, err = run_once(data, n_gpus, variant)
