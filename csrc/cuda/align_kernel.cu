@@ -123,13 +123,20 @@ __device__ __forceinline__ unsigned long long global_ns() {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 // Bounded wait for a flag written by a peer GPU (never an unbounded spin: a dead peer must not
-// hang this GPU). Returns false on timeout.
+// hang this GPU). Polls with relaxed loads — an acquire load per poll would
+// invalidate this SM's L1 every time — and the CALLER issues one acquire fence
+// (__threadfence_system) after its last flag. Returns false on timeout.
 __device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t epoch, unsigned long long timeout_ns) {
-    if ((int)(ld_acquire_sys(flag) - epoch) >= 0) return true;
+    if ((int)(ld_relaxed_sys(flag) - epoch) >= 0) return true;
     const unsigned long long t0 = global_ns();
     for (;;) {
-        if ((int)(ld_acquire_sys(flag) - epoch) >= 0) return true;
+        if ((int)(ld_relaxed_sys(flag) - epoch) >= 0) return true;
         __nanosleep(64);
         if (global_ns() - t0 > timeout_ns) return false;
     }
@@ -210,7 +217,8 @@ __device__ __forceinline__ bool fabric_bytes_ready(const KParams& p, const sa_bl
     volatile uint32_t* const cached = &s_all_here;
     if (*cached) return true;
     unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
-    if ((int)(ld_acquire_sys(my_ctl + kCtlAllHere) - p.epoch) >= 0) {
+    if ((int)(ld_relaxed_sys(my_ctl + kCtlAllHere) - p.epoch) >= 0) {
+        __threadfence_system();  // acquire: everything published before the flag is visible from here on
         *cached = 1u;
         if (p.timeline) atomicMin(&times[5], global_ns());
         return true;
@@ -219,6 +227,7 @@ __device__ __forceinline__ bool fabric_bytes_ready(const KParams& p, const sa_bl
     const uint32_t cb = hdr->chunk_bytes;
     for (uint32_t c = lo / cb; c <= (hi - 1u) / cb; ++c)
         if (!wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns)) return false;
+    __threadfence_system();  // one acquire fence for all the chunk flags just observed
     if (p.timeline) {
         atomicAdd(&times[6], 1ull);
         atomicAdd(&times[7], global_ns() - t0);
@@ -277,6 +286,7 @@ __device__ __forceinline__ void fabric_prologue(const KParams& p) {
             if (tid == 0) {
                 bool ok = wait_flag(my_ctl + kCtlFlags, p.epoch, p.timeout_ns);
                 if (ok) {
+                    __threadfence_system();  // the header must be read after its chunk's flag
                     const uint32_t npre = (hdr->off_seq2 + hdr->chunk_bytes - 1u) / hdr->chunk_bytes;
                     for (uint32_t c = 1; ok && c < npre; ++c) ok = wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns);
                 }
@@ -284,6 +294,7 @@ __device__ __forceinline__ void fabric_prologue(const KParams& p) {
                     s_abort = 1u;
                     atomicExch(my_ctl + kCtlError, 1u);
                 }
+                __threadfence_system();  // acquire side of the flags polled with relaxed loads
                 fence_proxy_async();
             }
             __syncthreads();
