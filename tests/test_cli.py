@@ -62,3 +62,8 @@ def test_gpu_mode_across_two_gpus_is_byte_identical(final_bin, shipped_inputs):
         out = subprocess.run([str(final_bin), "--gpus", "2"], stdin=open(path, "rb"), capture_output=True, timeout=600)
         assert out.returncode == 0, out.stderr.decode()[-2000:]
         assert out.stdout == gold.read_bytes()
+
+
+def test_zero_sequences_prints_nothing(final_bin):
+    out = subprocess.run([str(final_bin), "--cpu-oracle"], input=b"1 2 3 4 ABC 0\n", capture_output=True)
+    assert out.returncode == 0 and out.stdout == b""

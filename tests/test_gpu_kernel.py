@@ -221,3 +221,11 @@ def test_torch_ops_binding(solver, shipped_inputs):
         assert np.array_equal(out.cpu().numpy()[:, :3], solve_cpu(p, "fast"))
     text = shipped_inputs[1][0].read_bytes().decode("latin-1")
     assert np.array_equal(ops.solve_text(text, 0).numpy(), solve_cpu(Problem.from_file(shipped_inputs[1][0]), "fast"))
+
+
+def test_degenerate_problems(solver):
+    empty = Problem.parse(b"1 2 3 4 AB 0")
+    assert solver.solve(empty).shape == (0, 3)
+    none_fit = Problem.from_parts((1, 2, 3, 4), "AB", ["ABC", "ABCD"])  # every sequence longer than Seq1
+    assert solver.solve(none_fit).tolist() == [[-2147483648, 0, 0]] * 2
+    assert solver.solve_packed(solver.pack(none_fit)).tolist() == [[-2147483648, 0, 0]] * 2
