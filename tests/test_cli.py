@@ -67,3 +67,15 @@ def test_gpu_mode_across_two_gpus_is_byte_identical(final_bin, shipped_inputs):
 def test_zero_sequences_prints_nothing(final_bin):
     out = subprocess.run([str(final_bin), "--cpu-oracle"], input=b"1 2 3 4 ABC 0\n", capture_output=True)
     assert out.returncode == 0 and out.stdout == b""
+
+
+def test_python_module_entry_point(shipped_inputs):
+    import sys
+
+    path, gold = shipped_inputs[6]
+    out = subprocess.run([sys.executable, "-m", "mpi_openmp_cuda_b200", "--cpu"], stdin=open(path, "rb"), capture_output=True,
+                         cwd=ROOT, timeout=300)
+    assert out.returncode == 0, out.stderr.decode()[-1000:]
+    assert out.stdout == gold.read_bytes()
+    bad = subprocess.run([sys.executable, "-m", "mpi_openmp_cuda_b200", "--cpu"], input=b"1 2 3", capture_output=True, cwd=ROOT, timeout=300)
+    assert bad.returncode == 1 and bad.stdout == b""
