@@ -28,6 +28,7 @@
 static_assert(sizeof(sa_blob_header) == 256, "blob header must be 256 bytes");
 static_assert(sizeof(sa_seq_desc) == 16, "seq desc must be 16 bytes");
 static_assert(sizeof(sa_item) == 8, "item must be 8 bytes");
+static_assert(sizeof(sa_tile_item) == 32, "tile item must be 32 bytes");
 
 namespace sa {
 namespace {
@@ -323,6 +324,9 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     const uint32_t off_pairs = (uint32_t)off;
     if (use_stream) off += (uint64_t)sizeof(sa_item) * pairs.size();
     off = (off + 15) / 16 * 16;
+    const uint32_t off_tile_items = (uint32_t)off;
+    if (!use_pairs) off += (uint64_t)sizeof(sa_tile_item) * nitems;
+    off = (off + 31) / 32 * 32;
     const uint32_t off_seq2 = (uint32_t)off;
     std::vector<uint32_t> seq_off(nseq);
     for (uint32_t s = 0; s < nseq; ++s) {
@@ -475,6 +479,22 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
         for (const RankItem& it : per_rank[(size_t)r]) items[w++] = sa_item{it.seq, it.tile};
     }
     for (int r = world; r <= SA_MAX_WORLD; ++r) h->rank_first_item[r] = w;
+    h->off_tile_items = use_pairs ? 0u : off_tile_items;
+    if (!use_pairs) {
+        sa_tile_item* fat = reinterpret_cast<sa_tile_item*>(base + off_tile_items);
+        for (uint32_t i = 0; i < nitems; ++i) {
+            const sa_seq_desc& d = tab[items[i].seq];
+            fat[i].seq = items[i].seq;
+            fat[i].tile = items[i].tile;
+            fat[i].off = d.off;
+            fat[i].ndiag = d.ndiag;
+            fat[i].len = d.len;
+            fat[i].crow = d.crow;
+            fat[i].ntiles = d.ntiles;
+            fat[i].wd_log2 = d.wd_log2;
+            fat[i].home = d.home;
+        }
+    }
     return SA_OK;
 }
 
@@ -663,9 +683,17 @@ int sa_blob_score_items_cpu(const void* blob, size_t blob_bytes, uint32_t first_
         return SA_OK;
     }
     std::vector<int32_t> csum((size_t)kWarps * (kR + 1) * 32), cmax((size_t)kWarps * kR * 32);
+    const sa_tile_item* fat = reinterpret_cast<const sa_tile_item*>(b.base + b.h->off_tile_items);
     for (uint32_t it = first_item; it < last_item; ++it) {
         const uint32_t s = b.items[it].seq, tile = b.items[it].tile;
         const sa_seq_desc& sd = b.tab[s];
+        // the kernel reads the self-contained record; it must say what the two tables say
+        if (fat[it].seq != s || fat[it].tile != tile || fat[it].off != sd.off || fat[it].ndiag != sd.ndiag ||
+            fat[it].len != sd.len || fat[it].crow != sd.crow || fat[it].ntiles != sd.ntiles ||
+            fat[it].wd_log2 != sd.wd_log2 || fat[it].home != sd.home) {
+            set_error("sa_blob_score_items_cpu: tile item record disagrees with the item list / sequence table");
+            return SA_ERR_ARG;
+        }
         const unsigned char* s2 = b.base + sd.off;
         const uint32_t wd = 1u << sd.wd_log2, wr = kWarps / wd, crow = sd.crow;
         const uint32_t tn = kWarpDiag * wd, n0 = tile * tn;

@@ -51,7 +51,7 @@ struct KParams {
     uint32_t item_begin, item_end;
     uint32_t s2_cap, win_cap;   // shared-memory capacities (bytes, multiples of 16)
     uint32_t write_empty;       // 1: this launch writes the rows of candidate-free sequences
-    uint32_t h_off_lut, h_off_seq1, h_off_seqtab, h_off_items, h_nseq;  // header fields the host already knows (non-fabric)
+    uint32_t h_off_lut, h_off_seq1, h_off_seqtab, h_off_items, h_nseq, h_off_tile_items;  // header fields the host already knows (non-fabric)
     // ---- fabric (multi-GPU) launches only; see sa_cuda_fabric_solve
     uint32_t rank, world, epoch, use_mc;
     unsigned char* peer[SA_MAX_WORLD];  // every rank's symmetric buffer as mapped into this process
@@ -395,9 +395,11 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
     const uint32_t off_seq1 = kFabric ? (dead_on_arrival ? 0u : hdr->off_seq1) : p.h_off_seq1;
     const uint32_t off_lut = kFabric ? (dead_on_arrival ? 0u : hdr->off_lut) : p.h_off_lut;
     const uint32_t nseq_all = kFabric ? (dead_on_arrival ? 0u : hdr->nseq) : p.h_nseq;
+    const uint32_t off_fat = kFabric ? (dead_on_arrival ? 0u : hdr->off_tile_items) : p.h_off_tile_items;
     const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + off_seqtab);
-    const sa_item* const items = reinterpret_cast<const sa_item*>(p.blob + off_items);
+    const sa_tile_item* const fat = reinterpret_cast<const sa_tile_item*>(p.blob + off_fat);
     const unsigned char* const seq1g = p.blob + off_seq1;
+    (void)off_items;
     const uint32_t item_begin = kFabric ? (dead_on_arrival ? 0u : hdr->rank_first_item[p.rank]) : p.item_begin;
     const uint32_t item_end = kFabric ? (dead_on_arrival ? 0u : hdr->rank_first_item[p.rank + 1]) : p.item_end;
     int4* const out = kFabric ? reinterpret_cast<int4*>(p.peer[0] + p.off_out) : p.out;
@@ -415,7 +417,7 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
             uint32_t it = item_begin + (first ? blockIdx.x : gridDim.x + atomicAdd(&my_ctl[kCtlNext], 1u));
             if (!kFabric && first && hdr->magic != SA_BLOB_MAGIC) it = 0xFFFFFFFFu;  // never walk memory that is not a packed problem
             if (kFabric && p.rank != 0 && it < item_end) {  // this sequence's letters may still be in flight
-                const sa_seq_desc d = seqtab[items[it].seq];
+                const sa_tile_item d = fat[it];
                 const uint32_t bytes = ((uint32_t)d.crow * ((uint32_t)kWarps >> d.wd_log2) + 15u) & ~15u;
                 const bool ok = fabric_bytes_ready(p, hdr, my_ctl, d.off, d.off + bytes);
                 if (!ok) {
@@ -430,8 +432,8 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
         const uint32_t item = ctl[0];
         if (item >= item_end || (kFabric && s_abort != 0u)) break;
 
-        const uint32_t seq = items[item].seq, tile = items[item].tile;
-        const sa_seq_desc sd = seqtab[seq];
+        const sa_tile_item sd = fat[item];  // one self-contained 32-byte record per item
+        const uint32_t seq = sd.seq, tile = sd.tile;
         const uint32_t wd_log2 = sd.wd_log2, wd = 1u << wd_log2, wr = (uint32_t)kWarps >> wd_log2;
         const uint32_t crow = sd.crow, rows_padded = crow * wr;
         const uint32_t tn = (uint32_t)SA_DIAG_PER_WARP << wd_log2, n0 = tile * tn;
@@ -1165,6 +1167,7 @@ int sa_cuda_solve_blob(const void* d_blob, const sa_blob_header* h, int32_t* d_o
     p.h_off_seqtab = h->off_seqtab;
     p.h_off_items = h->off_items;
     p.h_nseq = h->nseq;
+    p.h_off_tile_items = h->off_tile_items;
     p.s2_cap = (h->max_rows_padded + 15u) & ~15u;
     p.win_cap = (h->max_window_bytes + 15u) & ~15u;
     p.write_empty = 1;

@@ -170,7 +170,8 @@ typedef struct sa_blob_header {
     uint32_t value_range;  /* max - min of the same set                               */
     uint32_t off_pairs;    /* STREAM: sa_item[npairs] = (first, second or SA_NO_SEQ)  */
     uint32_t npairs;
-    uint32_t reserved[16];
+    uint32_t off_tile_items; /* TILE: sa_tile_item[nitems], same order as the item list */
+    uint32_t reserved[15];
 } sa_blob_header; /* 256 bytes */
 
 typedef struct sa_seq_desc {
@@ -182,6 +183,18 @@ typedef struct sa_seq_desc {
     uint8_t wd_log2;   /* log2(warps laid across offsets); rows get 16>>wd_log2 */
     uint8_t home;      /* rank holding this sequence's key + arrival counter   */
 } sa_seq_desc; /* 16 bytes */
+
+/* TILE mode: everything a CTA needs to start an item in ONE 32-byte record (the item list and the
+ * sequence table stay, for tools and for the other modes): one dependent read of cold memory
+ * instead of two before the first TMA copy can be issued. */
+typedef struct sa_tile_item {
+    uint32_t seq, tile;
+    uint32_t off;     /* = seqtab[seq].off   */
+    int32_t ndiag;    /* = seqtab[seq].ndiag */
+    uint16_t len, crow, ntiles;
+    uint8_t wd_log2, home;
+    uint32_t pad[2];
+} sa_tile_item; /* 32 bytes */
 
 typedef struct sa_item {
     uint32_t seq;  /* TILE: sequence          PAIR: first sequence     STREAM: pair index    */

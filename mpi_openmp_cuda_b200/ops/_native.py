@@ -33,7 +33,7 @@ class BlobHeader(C.Structure):
         ("max_rows_padded", C.c_uint32), ("max_window_bytes", C.c_uint32), ("chunk_bytes", C.c_uint32), ("nchunks", C.c_uint32), ("pad0", C.c_uint32),
         ("total_cells", C.c_uint64), ("padded_cells", C.c_uint64),
         ("world", C.c_uint32), ("rank_first_item", C.c_uint32 * (SA_MAX_WORLD + 1)),
-        ("value_min", C.c_int32), ("value_range", C.c_uint32), ("off_pairs", C.c_uint32), ("npairs", C.c_uint32), ("reserved", C.c_uint32 * 16),
+        ("value_min", C.c_int32), ("value_range", C.c_uint32), ("off_pairs", C.c_uint32), ("npairs", C.c_uint32), ("off_tile_items", C.c_uint32), ("reserved", C.c_uint32 * 15),
     ]
 
 
