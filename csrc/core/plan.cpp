@@ -367,14 +367,14 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
             for (const Pair& pr : pairs) per_rank[0].push_back({pr.a, pr.b});
         }
     } else {
-        std::vector<uint32_t> order(nseq);
-        std::iota(order.begin(), order.end(), 0u);
-        std::stable_sort(order.begin(), order.end(),
+        std::vector<uint32_t> by_cost(nseq);
+        std::iota(by_cost.begin(), by_cost.end(), 0u);
+        std::stable_sort(by_cost.begin(), by_cost.end(),
                          [&](uint32_t a, uint32_t b) { return plans[a].item_cost > plans[b].item_cost; });
         std::vector<uint64_t> load((size_t)world, 0);
         const bool by_tile = world > 1 && nseq < 2u * (uint32_t)world;
         auto lightest = [&]() { return (int)(std::min_element(load.begin(), load.end()) - load.begin()); };
-        for (uint32_t s : order) {
+        for (uint32_t s : by_cost) {
             const SeqPlan& sp = plans[s];
             if (sp.ntiles == 0) continue;
             if (!by_tile) {
