@@ -29,6 +29,10 @@ g++ -O2 -o "$OUT/bin/mpiexec" "$HERE/mpi_shim/mpiexec.cpp" -I"$HERE/mpi_shim" -l
 g++ -O2 -o "$OUT/bin/bench_coll" "$HERE/mpi_shim/bench_coll.cpp" -I"$HERE/mpi_shim" -L"$OUT/shim" -lmpishim -lpthread \
     -Wl,-rpath,'$ORIGIN/../shim' || exit 1
 
+echo "== step 2b: CUPTI injection probe (device time of the unmodified binary's kernels)"
+g++ -O2 -fPIC -shared -o "$OUT/shim/libcuptiinject.so" "$HERE/cupti_inject/inject.cpp" -I"$CUDA_HOME/include" \
+    -L"$CUDA_HOME/lib64" -lcupti -Wl,-rpath,"$CUDA_HOME/lib64" || echo "cupti probe not built (device time falls back to wall - start-up)"
+
 echo "== step 3: reference sources (verbatim)"
 if [ -d "$REF_SRC" ]; then
     cp "$REF_SRC/main.c" "$REF_SRC/cudaFunctions.cu" "$REF_SRC/myProto.h" "$REF_SRC/makefile" "$OUT/src/"

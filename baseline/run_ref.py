@@ -15,9 +15,11 @@ from __future__ import annotations
 import argparse
 import json
 import os
+import shutil
 import statistics
 import subprocess
 import sys
+import tempfile
 import time
 from pathlib import Path
 
@@ -40,23 +42,52 @@ def ensure_built() -> str | None:
     return None
 
 
-def run_once(input_bytes: bytes, np_: int, variant: str = "final", timeout: float = 3600.0):
+def run_once(input_bytes: bytes, np_: int, variant: str = "final", timeout: float = 3600.0, probe: bool = True):
+    """One whole `mpiexec -np N ./final < input` run. Returns (wall_s, rc, stdout, stderr, device) where
+    `device` is the CUPTI probe's per-rank record list (baseline/cupti_inject) or None."""
     env = dict(os.environ)
     env["OMP_NUM_THREADS"] = "1"  # the reference's parallel stdin loop scrambles rows otherwise (main.c:96-108)
     env["SHIM_GPUS"] = ",".join(str(i) for i in range(np_))  # it always opens device 0 (cudaFunctions.cu:209)
     env.pop("CUDA_VISIBLE_DEVICES", None)
+    inject = REF / "shim" / "libcuptiinject.so"
+    tmpdir = None
+    if probe and inject.exists():
+        tmpdir = tempfile.mkdtemp(prefix="refcupti_")
+        env["CUDA_INJECTION64_PATH"] = str(inject)
+        env["REF_CUPTI_OUT"] = os.path.join(tmpdir, "rank")
+    else:
+        env.pop("CUDA_INJECTION64_PATH", None)
     cmd = [str(REF / "bin" / "mpiexec"), "-np", str(np_), str(REF / "bin" / variant)]
     t0 = time.perf_counter()
     proc = subprocess.run(cmd, input=input_bytes, capture_output=True, env=env, timeout=timeout)
     dt = time.perf_counter() - t0
-    return dt, proc.returncode, proc.stdout, proc.stderr
+    device = None
+    if tmpdir:
+        recs = []
+        for f in sorted(os.listdir(tmpdir)):
+            try:
+                recs.append(json.loads(open(os.path.join(tmpdir, f)).read()))
+            except Exception:
+                pass
+        shutil.rmtree(tmpdir, ignore_errors=True)
+        recs = [r for r in recs if r.get("kernels", 0) > 0]
+        device = recs or None
+    return dt, proc.returncode, proc.stdout, proc.stderr, device
+
+
+def device_ms(device) -> float | None:
+    """Reference device time of one run: per rank the sum of its kernels' GPU durations (they are
+    serialised by a cudaDeviceSynchronize each, cudaFunctions.cu:218), then the max over ranks."""
+    if not device:
+        return None
+    return max(r["kernel_ns"] for r in device) * 1e-6
 
 
 def expected_output(input_bytes: bytes) -> bytes:
-    from mpi_openmp_cuda_b200 import Problem, format_results
-    from mpi_openmp_cuda_b200.ops.oracle import solve_cpu
+    """The section 8.2 contract, restated in numpy (baseline/refgen.py): nothing of the repo's native code."""
+    from baseline import refgen
 
-    return format_results(solve_cpu(Problem.parse(input_bytes), "fast"))
+    return refgen.format_results(refgen.solve(*refgen.parse_text(input_bytes)))
 
 
 def diff_rows(got: bytes, want: bytes) -> dict:
@@ -66,23 +97,27 @@ def diff_rows(got: bytes, want: bytes) -> dict:
 
 
 def bench_reference(args, rank: int, world: int):
-    """`bench.py --impl reference`: same input, same metric, the reference's own code path."""
+    """`bench.py --impl reference`: same input bytes, same metric, the reference's own code path
+    (`mpiexec -np N ./final < input`, makefile:11). Loads no native code of this repository."""
     if rank != 0:
         return None
     why = ensure_built()
     if why:
         return {"impl": "reference", "unavailable": why}
-    from bench import build_problem  # same config as our arm
+    from baseline import refgen
+    from baseline.contract import METRIC, MODEL, UNIT
 
     n_gpus = args.gpus
-    problem = build_problem(args, n_gpus)
-    cands = problem.candidates()
-    data = problem.serialize() if args.scale * n_gpus > 1 else (ROOT / "data" / args.input).read_bytes()
+    total_scale = args.scale * n_gpus
+    data = refgen.scaled_text(ROOT / "data" / args.input, total_scale, seed=1)
+    weights, seq1, seqs = refgen.parse_text(data)
+    cands = refgen.candidates(seq1, seqs)
     variant = os.environ.get("REF_VARIANT", "final")
-    budget_s = float(os.environ.get("REF_BUDGET_S", "300"))
+    budget_s = float(os.environ.get("REF_BUDGET_S", "800"))
     floor_input = (ROOT / "data" / "input5.txt").read_bytes()
+    t_begin = time.perf_counter()
     try:
-        t_first, rc, out, err = run_once(data, n_gpus, variant)
+        t_first, rc, out, err, dev_first = run_once(data, n_gpus, variant)
     except subprocess.TimeoutExpired:
         return {"impl": "reference", "unavailable": "the reference did not finish one run of this input in 3600 s"}
     if rc != 0:
@@ -90,28 +125,53 @@ def bench_reference(args, rank: int, world: int):
     check = diff_rows(out, expected_output(data))
     steps, warmup = args.steps, args.warmup
     if (steps + warmup) * t_first > budget_s:  # keep the arm inside the box's time budget; say so
-        warmup = 1 if t_first * (steps + 1) <= budget_s else 0
+        warmup = min(warmup, 1)
         steps = max(1, min(steps, int(budget_s / max(t_first, 1e-3)) - warmup))
     for _ in range(max(0, warmup - 1)):  # the first run above already was one warm-up (JIT cache, page cache)
         run_once(data, n_gpus, variant)
-    times = [run_once(data, n_gpus, variant)[0] for _ in range(steps)]
-    floor = min(run_once(floor_input, n_gpus, variant)[0] for _ in range(3))
-    ms = statistics.fmean(times) * 1e3
+    runs = [run_once(data, n_gpus, variant) for _ in range(steps)]
+    wall_ms = statistics.fmean(r[0] for r in runs) * 1e3
+    dev = [device_ms(r[4]) for r in runs]
+    have_dev = all(d is not None for d in dev)
+    # start-up floor (process + CUDA context + JIT-cache lookup) on the 9-candidate input5.txt
+    floor = run_once(floor_input, n_gpus, variant)[0]
+    floor_plain = run_once(floor_input, n_gpus, variant, probe=False)[0]
+    if have_dev:
+        ms = statistics.fmean(dev)
+        timing = ("GPU timestamps of the reference's own kernels (CUPTI activity records through CUDA_INJECTION64_PATH; "
+                  "no replay, no source change), summed per rank, max over ranks")
+    else:
+        ms = wall_ms - floor * 1e3
+        timing = "wall clock of the whole run minus the start-up floor measured on input5.txt (the CUPTI probe gave no records)"
+    last = runs[-1][4] or []
+    h2d = sum(r.get("h2d_bytes", 0) for r in last)
+    d2h = sum(r.get("d2h_bytes", 0) for r in last)
     return {
         "impl": "reference",
-        "metric": "candidates/s (one full solve of the input; wall clock of the whole `mpiexec -np N ./final < input` run)",
-        "value": cands / (ms * 1e-3), "unit": "candidates/s", "n_gpus": n_gpus,
+        "metric": METRIC,
+        "value": cands / (ms * 1e-3), "unit": UNIT, "n_gpus": n_gpus,
         "steps": steps, "warmup": warmup, "steps_requested": args.steps, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "int32", "data": f"data/{args.input} x{args.scale * n_gpus}",
-        "config": {"model": "exhaustive (n,k) alignment search", "input": args.input, "scale_per_gpu": args.scale,
-                   "nseq": problem.nseq, "candidates": cands, "parallelism": f"mpi{n_gpus} (stand-in MPI, one rank per GPU)",
+        "dtype": "int32", "data": f"shipped reference input data/{args.input}" + ("" if total_scale == 1 else f" replicated x{total_scale} with random substitutions (synthetic)"),
+        "config": {"model": MODEL, "input": args.input, "scale_per_gpu": args.scale,
+                   "nseq": len(seqs), "len1": len(seq1), "candidates": cands, "global_batch": len(seqs), "seq_len": len(seq1),
+                   "parallelism": f"dp{n_gpus}",
+                   "launcher": f"mpiexec -np {n_gpus} ./final < input (stand-in MPI, one rank per GPU)",
                    "variant": variant + (" (makefile flags: sm_52 SASS + PTX JIT)" if variant == "final" else " (-arch=sm_100)"),
                    "OMP_NUM_THREADS": 1},
+        "timing": timing,
+        "e2e": {"value": cands / (wall_ms * 1e-3), "unit": UNIT, "ms_per_step": wall_ms,
+                "what": "wall clock of the whole `mpiexec -np N ./final < input` run: the only interface the reference has "
+                        "(process start, CUDA context, stdin parse, H2D, its kernels, D2H, print)",
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "startup_floor_ms": floor * 1e3, "ms_per_step_minus_startup": wall_ms - floor * 1e3},
+        "gpu_launches": sum(r.get("kernels", 0) for r in last) * steps if last else None,
+        "kernels_per_step": sum(r.get("kernels", 0) for r in last) if last else None,
+        "device_ms_per_rank_last_step": [round(r["kernel_ns"] * 1e-6, 3) for r in last],
         "first_run_ms": t_first * 1e3, "startup_floor_ms": floor * 1e3,
-        "ms_per_step_minus_startup": ms - floor * 1e3,
+        "probe_overhead_ms": (floor - floor_plain) * 1e3,
         "output_check": check,
-        "timing": "wall clock, whole process (the reference has no timers, SURVEY.md 5.1)",
+        "arm_wall_s": time.perf_counter() - t_begin,
     }
 
 
@@ -133,16 +193,17 @@ def main():
             for i in a.inputs:
                 data = (ROOT / "data" / f"input{i}.txt").read_bytes()
                 want = expected_output(data)
-                ts, rc, out, err = [], 0, b"", b""
+                ts, rc, out, err, dev = [], 0, b"", b"", None
                 for _ in range(a.repeat):
                     try:
-                        dt, rc, out, err = run_once(data, np_, variant, timeout=1800)
+                        dt, rc, out, err, dev = run_once(data, np_, variant, timeout=1800)
                     except subprocess.TimeoutExpired:
                         rc, dt = -9, 1800.0
                     ts.append(dt)
                     if rc != 0:
                         break
                 row = {"variant": variant, "np": np_, "input": i, "rc": rc, "times_s": ts, "best_s": min(ts),
+                       "device_ms": device_ms(dev), "kernels": sum(r.get("kernels", 0) for r in dev) if dev else None,
                        **diff_rows(out, want), "stderr_tail": err[-160:].decode("latin-1", "replace")}
                 rows.append(row)
                 print(json.dumps(row), flush=True)
