@@ -17,7 +17,7 @@ CUDA_SRC := csrc/cuda/align_kernel.cu csrc/cuda/fabric_bench.cu
 CORE_LIB := $(LIBDIR)/libseqalign_core.so
 CUDA_LIB := $(LIBDIR)/libseqalign_cuda.so
 
-.PHONY: build core cuda clean run runOn2 test sass asan tsan
+.PHONY: build core cuda clean run runOn2 test sass asan tsan microbench
 
 build: core cuda final
 
@@ -36,6 +36,12 @@ $(CUDA_LIB): $(CUDA_SRC) $(wildcard csrc/cuda/*.cuh) include/seqalign.h $(CORE_L
 final: csrc/host/final_main.cpp $(CORE_LIB) $(CUDA_LIB)
 	$(CXX) $(CXXFLAGS) -o $@ csrc/host/final_main.cpp -L$(LIBDIR) -lseqalign_core -ldl \
 	    -Wl,-rpath,'$$ORIGIN/$(LIBDIR)'
+
+# Pipe-rate micro-benchmarks (LDS / IADD3 / IMAD / VIMNMX / tcgen05.ld): profiles/MEASURED_PIPES.json
+microbench: build/microbench
+build/microbench: csrc/cuda/microbench.cu
+	@mkdir -p build
+	$(NVCC) -O3 -std=c++17 $(GENCODE) -lineinfo -o $@ $<
 
 clean:
 	rm -f final $(LIBDIR)/*.so csrc/**/*.o

@@ -25,7 +25,8 @@
 
 #include "core.hpp"
 
-static_assert(sizeof(sa_blob_header) == 256, "blob header must be 256 bytes");
+static_assert(sizeof(sa_blob_header) == 1024, "blob header must be 1024 bytes");
+static_assert(sizeof(sa_pair_rec) == 32, "pair record must be 32 bytes");
 static_assert(sizeof(sa_seq_desc) == 16, "seq desc must be 16 bytes");
 static_assert(sizeof(sa_item) == 8, "item must be 8 bytes");
 static_assert(sizeof(sa_tile_item) == 32, "tile item must be 32 bytes");
@@ -276,6 +277,34 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     for (uint32_t s = 0; s < nseq; ++s) {
         plans[s] = plan_sequence(len1, (uint32_t)p->seq2[s].size());
         total_cells += (uint64_t)sa_problem_candidates(p, (int32_t)s);
+    }
+    if (!use_pairs) {
+        // Latency mode. plan_sequence minimises each sequence's TOTAL padded cost, which is right when
+        // items outnumber SMs. When the whole problem is fewer items than SMs, the solve time is the
+        // LONGEST item (an SM scans one row of a 16-warp CTA per ~144 shared-memory wavefronts, so an
+        // item lasts ~crow row-steps plus ~2 steps per row chunk it merges) while most SMs idle: split
+        // the longest item's rows over more warps (narrower offset tiles, more of them) until the SMs
+        // are used up. The reference scores a whole row in ONE block (cudaFunctions.cu:210-216).
+        const uint64_t slots = (uint64_t)SA_PLAN_SMS * (uint64_t)world;
+        auto steps = [](const SeqPlan& sp) { return (uint64_t)sp.crow + 2ull * (kWarps >> sp.wd_log2); };
+        uint64_t nit = 0;
+        for (uint32_t s = 0; s < nseq; ++s) nit += plans[s].ntiles;
+        while (nit < slots) {
+            uint32_t worst = nseq;
+            for (uint32_t s = 0; s < nseq; ++s)
+                if (plans[s].ntiles && (worst == nseq || steps(plans[s]) > steps(plans[worst]))) worst = s;
+            if (worst == nseq || plans[worst].wd_log2 == 0) break;  // the longest item cannot be split further
+            SeqPlan sp = plans[worst];
+            sp.wd_log2 -= 1;
+            const uint32_t wr = kWarps >> sp.wd_log2, tn = kWarpDiag << sp.wd_log2;
+            const uint32_t d = sp.ndiag == 0 ? 1u : (uint32_t)sp.ndiag;
+            sp.crow = round_up((sp.len + wr - 1) / wr, kU);
+            sp.ntiles = (d + tn - 1) / tn;
+            sp.item_cost = (uint64_t)tn * wr * sp.crow;
+            if (steps(sp) >= steps(plans[worst]) || nit - plans[worst].ntiles + sp.ntiles > slots) break;
+            nit += sp.ntiles - plans[worst].ntiles;
+            plans[worst] = sp;
+        }
     }
     if (use_pairs) {
         for (const Pair& pr : pairs) {

@@ -24,6 +24,7 @@
 #include <climits>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 #include <new>
 #include <string>
@@ -155,6 +156,47 @@ __device__ __forceinline__ uint32_t byte_of(uint32_t lo, uint32_t hi, int k) {  
 // (measured: STREAM +6 %, PAIR +2 %; the int32 TILE kernel is 7 % slower with it, so it keeps byte_of).
 __device__ __forceinline__ uint32_t byte_of_prmt(uint32_t lo, uint32_t hi, int k) {
     return __byte_perm(k < 4 ? lo : hi, 0u, 0x4440u | (uint32_t)(k & 3));
+}
+
+
+// ------------------------------------------------------------------ the scan step ("difference form")
+//
+// What a lane carries for its R = 8 offsets is NOT the nine running prefixes P[0..8] of the
+// neighbouring diagonals but their eight neighbour differences D[r] = P[r] - P[r+1] — the quantity
+// whose running maximum is wanted — plus ONE running total (P8, the ninth diagonal). Per cell that
+// is one 3-input add (D += v[r] - v[r+1], a single IADD3) and half a 3-input max (two rows per
+// VIMNMX3) instead of add + subtract + max: the ALU pipe issues one instruction every other clock
+// per SM sub-partition (profiles/MEASURED_PIPES.json), and it was the binding unit of the P-form
+// loop. The nine totals are rebuilt once per item from P8 and the final differences (to_prefixes).
+// u16x2: both halves are biased to stay non-negative (D starts at BIG per half, values are
+// v - vmin >= 0), so the 32-bit adds never carry or borrow between the halves as long as
+// rows * value_range <= 32767 — the planner's limit; the CPU walk re-checks every step.
+constexpr uint32_t kBig = 32767u, kBig2 = kBig | (kBig << 16);
+
+// Eight rows of one lane: A[k] points at the profile word of row 0 for the letter under diagonal k.
+__device__ __forceinline__ void scan8_u16x2(const unsigned char* const (&A)[2 * kU], uint32_t (&D)[kR], uint32_t (&best)[kR],
+                                            uint32_t& P8) {
+#pragma unroll
+    for (int u = 0; u < kU; u += 2) {
+        uint32_t v[kR + 1], w[kR + 1];
+#pragma unroll
+        for (int r = 0; r <= kR; ++r) v[r] = *reinterpret_cast<const uint32_t*>(A[u + r] + u * (SA_ALPHABET * 4));
+#pragma unroll
+        for (int r = 0; r <= kR; ++r) w[r] = *reinterpret_cast<const uint32_t*>(A[u + 1 + r] + (u + 1) * (SA_ALPHABET * 4));
+#pragma unroll
+        for (int r = 0; r < kR; ++r) {
+            const uint32_t d0 = D[r] + v[r] - v[r + 1];
+            D[r] = d0 + w[r] - w[r + 1];
+            best[r] = __vimax3_u16x2(best[r], d0, D[r]);
+        }
+        P8 += v[kR] + w[kR];
+    }
+}
+// P[r] = P[r+1] + D[r] (bias removed): the nine biased prefix totals of the lane's diagonals.
+__device__ __forceinline__ void to_prefixes_u16x2(const uint32_t (&D)[kR], uint32_t P8, uint32_t (&P)[kR + 1]) {
+    P[kR] = P8;
+#pragma unroll
+    for (int r = kR - 1; r >= 0; --r) P[r] = P[r + 1] + D[r] - kBig2;
 }
 
 // First k in [0, m) whose candidate (n fixed) reaches `bestv` — the reference's strict-'>' update
@@ -344,6 +386,7 @@ __device__ __forceinline__ void launch_epilogue(const KParams& p) {
                 }
             }
         }
+        if (p.timeline) atomicMax(&times[16], global_ns());
     }
 }
 
@@ -374,7 +417,8 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
     uint32_t parity = 0;
     uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
     unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
-    const bool timeline = kFabric && p.timeline != 0u && !prologue_done;
+    const bool timeline = p.timeline != 0u && (!kFabric || !prologue_done);
+    const bool tl_any = p.timeline != 0u;  // slots 11..15: latest CTA to reach each phase of its FIRST item
     if (timeline && tid == 0) atomicMin(&times[0], global_ns());
 
     if (tid == 0) {
@@ -427,6 +471,7 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
                 fence_proxy_async();
             }
             ctl[0] = it;
+            if (tl_any && first) atomicMax(&times[11], global_ns());
         }
         __syncthreads();  // also: every read of s2/win/csum of the previous item is done
         const uint32_t item = ctl[0];
@@ -452,7 +497,9 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
         }
         mbar_wait(bar, parity);
         parity ^= 1u;
+        const bool was_first = first;
         first = false;
+        if (tl_any && was_first && tid == 0) atomicMax(&times[12], global_ns());
 
         // ---- scan: this warp = offset group g, row chunk q
         {
@@ -460,11 +507,9 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
             const uint32_t d0 = g * SA_DIAG_PER_WARP + lane * kR;
             const unsigned char* wp = win + d0 + q * crow;  // letters of column (row + d0 + k)
             const unsigned char* sp = s2 + q * crow;
-            int P[kR + 1], best[kR];
+            int D[kR], best[kR], P8 = 0;  // difference form, see scan8_u16x2
 #pragma unroll
-            for (int r = 0; r <= kR; ++r) P[r] = 0;
-#pragma unroll
-            for (int r = 0; r < kR; ++r) best[r] = kNeg;
+            for (int r = 0; r < kR; ++r) D[r] = 0, best[r] = kNeg;
             uint2 lw0 = *reinterpret_cast<const uint2*>(wp);
             for (uint32_t row = 0; row < crow; row += kU) {
                 const uint2 lw1 = *reinterpret_cast<const uint2*>(wp + row + kU);
@@ -476,24 +521,35 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
                     L[kU + k] = byte_of(lw1.x, lw1.y, k);
                 }
 #pragma unroll
-                for (int u = 0; u < kU; ++u) {
-                    const unsigned char* lrow = lut_b + byte_of(sc.x, sc.y, u) * (SA_ALPHABET * 4u);
-                    int v[kR + 1];
+                for (int u = 0; u < kU; u += 2) {
+                    const unsigned char* lrow0 = lut_b + byte_of(sc.x, sc.y, u) * (SA_ALPHABET * 4u);
+                    const unsigned char* lrow1 = lut_b + byte_of(sc.x, sc.y, u + 1) * (SA_ALPHABET * 4u);
+                    int v[kR + 1], w[kR + 1];
 #pragma unroll
-                    for (int r = 0; r <= kR; ++r) v[r] = *reinterpret_cast<const int*>(lrow + L[u + r]);
+                    for (int r = 0; r <= kR; ++r) v[r] = *reinterpret_cast<const int*>(lrow0 + L[u + r]);
 #pragma unroll
-                    for (int r = 0; r <= kR; ++r) P[r] += v[r];
+                    for (int r = 0; r <= kR; ++r) w[r] = *reinterpret_cast<const int*>(lrow1 + L[u + 1 + r]);
 #pragma unroll
-                    for (int r = 0; r < kR; ++r) best[r] = max(best[r], P[r] - P[r + 1]);
+                    for (int r = 0; r < kR; ++r) {
+                        const int d0 = D[r] + v[r] - v[r + 1];
+                        D[r] = d0 + w[r] - w[r + 1];
+                        best[r] = __vimax3_s32(best[r], d0, D[r]);
+                    }
+                    P8 += v[kR] + w[kR];
                 }
                 lw0 = lw1;
             }
+            int P[kR + 1];
+            P[kR] = P8;
+#pragma unroll
+            for (int r = kR - 1; r >= 0; --r) P[r] = P[r + 1] + D[r];
 #pragma unroll
             for (int r = 0; r <= kR; ++r) csum[(warp * (kR + 1) + r) * 32 + lane] = P[r];
 #pragma unroll
             for (int r = 0; r < kR; ++r) cmax[(warp * kR + r) * 32 + lane] = best[r];
         }
         __syncthreads();
+        if (tl_any && was_first && tid == 0) atomicMax(&times[13], global_ns());
 
         // ---- merge row chunks in order, score every offset of the tile, keep the best
         unsigned long long mykey = 0ull;
@@ -547,6 +603,7 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
         }
         __syncthreads();
 
+        if (tl_any && was_first && tid == 0) atomicMax(&times[14], global_ns());
         // ---- last tile of this sequence: find the first k on the winning diagonal
         if (ctl[1]) {
             if (tid == 0 && sd.ntiles != 1) {
@@ -570,9 +627,11 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
                     *keyp = 0ull;  // leave the scratch zeroed for the next launch
                     *cntp = 0u;
                 }
+                if (tl_any && was_first) atomicMax(&times[15], global_ns());
             }
         }
     }
+    if (tl_any && tid == 0) atomicMax(&times[2], global_ns());
 
     if (!epilogue_later) launch_epilogue<kFabric>(p);
 }
@@ -614,7 +673,7 @@ __global__ void __launch_bounds__(kThreads, 1) sa_score_pair_kernel(const KParam
     const sa_item* const items = reinterpret_cast<const sa_item*>(p.blob + hdr->off_items);
     const int* const lut_i = reinterpret_cast<const int*>(lut_b);
     const int vmin = hdr->value_min;
-    constexpr uint32_t BIG = 32767u, BIG2 = BIG | (BIG << 16);
+    constexpr uint32_t BIG = kBig;
     const uint32_t bar = smem_u32(mbar);
     uint32_t parity = 0;
 
@@ -678,11 +737,9 @@ __global__ void __launch_bounds__(kThreads, 1) sa_score_pair_kernel(const KParam
             {
                 const unsigned char* wp = seq1s + n0 + d0 + q * crow;
                 const unsigned char* pb = reinterpret_cast<const unsigned char*>(prof) + (size_t)q * crow * (SA_ALPHABET * 4u);
-                uint32_t P[kR + 1], best[kR];
+                uint32_t D[kR], best[kR], P8 = 0u;
 #pragma unroll
-                for (int r = 0; r <= kR; ++r) P[r] = 0u;
-#pragma unroll
-                for (int r = 0; r < kR; ++r) best[r] = 0u;
+                for (int r = 0; r < kR; ++r) D[r] = kBig2, best[r] = 0u;
                 uint2 lw0 = *reinterpret_cast<const uint2*>(wp);
                 for (uint32_t row = 0; row < crow; row += kU) {
                     const uint2 lw1 = *reinterpret_cast<const uint2*>(wp + row + kU);
@@ -692,20 +749,12 @@ __global__ void __launch_bounds__(kThreads, 1) sa_score_pair_kernel(const KParam
                         A[k] = pb + byte_of_prmt(lw0.x, lw0.y, k);
                         A[kU + k] = pb + byte_of_prmt(lw1.x, lw1.y, k);
                     }
-#pragma unroll
-                    for (int u = 0; u < kU; ++u) {
-                        uint32_t v[kR + 1];
-#pragma unroll
-                        for (int r = 0; r <= kR; ++r)
-                            v[r] = *reinterpret_cast<const uint32_t*>(A[u + r] + u * (SA_ALPHABET * 4));
-#pragma unroll
-                        for (int r = 0; r <= kR; ++r) P[r] += v[r];
-#pragma unroll
-                        for (int r = 0; r < kR; ++r) best[r] = __vmaxu2(best[r], P[r] + BIG2 - P[r + 1]);
-                    }
+                    scan8_u16x2(A, D, best, P8);
                     lw0 = lw1;
                     pb += kU * (SA_ALPHABET * 4u);
                 }
+                uint32_t P[kR + 1];
+                to_prefixes_u16x2(D, P8, P);
 #pragma unroll
                 for (int r = 0; r <= kR; ++r) csum[(warp * (kR + 1) + r) * 32 + lane] = P[r];
 #pragma unroll
@@ -852,7 +901,7 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
     const sa_item* const items = reinterpret_cast<const sa_item*>(p.blob + hdr->off_items);
     const sa_item* const pairs = reinterpret_cast<const sa_item*>(p.blob + hdr->off_pairs);
     const int vmin = hdr->value_min;
-    constexpr uint32_t BIG = 32767u, BIG2 = BIG | (BIG << 16);
+    constexpr uint32_t BIG = kBig;
     const uint32_t bar = smem_u32(mbar);
     uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
     int4* const out = kFabric ? reinterpret_cast<int4*>(p.peer[0] + p.off_out) : p.out;
@@ -921,11 +970,9 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
             if (!__shfl_sync(0xFFFFFFFFu, ok, 0)) break;
         }
 
-        uint32_t P[kR + 1], best[kR];
+        uint32_t D[kR], best[kR], P8 = 0u;
 #pragma unroll
-        for (int r = 0; r <= kR; ++r) P[r] = 0u;
-#pragma unroll
-        for (int r = 0; r < kR; ++r) best[r] = 0u;
+        for (int r = 0; r < kR; ++r) D[r] = kBig2, best[r] = 0u;
         const unsigned char* wp = seq1s + n0 + d0;
         uint2 lw0 = *reinterpret_cast<const uint2*>(wp);
         for (uint32_t rb = 0; rb < rows; rb += SA_STREAM_ROW_BLOCK) {
@@ -962,22 +1009,15 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
                     A[k] = pb + byte_of_prmt(lw0.x, lw0.y, k);
                     A[kU + k] = pb + byte_of_prmt(lw1.x, lw1.y, k);
                 }
-#pragma unroll
-                for (int u = 0; u < kU; ++u) {
-                    uint32_t v[kR + 1];
-#pragma unroll
-                    for (int r = 0; r <= kR; ++r) v[r] = *reinterpret_cast<const uint32_t*>(A[u + r] + u * (SA_ALPHABET * 4));
-#pragma unroll
-                    for (int r = 0; r <= kR; ++r) P[r] += v[r];
-#pragma unroll
-                    for (int r = 0; r < kR; ++r) best[r] = __vmaxu2(best[r], P[r] + BIG2 - P[r + 1]);
-                }
+                scan8_u16x2(A, D, best, P8);
                 lw0 = lw1;
                 pb += kU * (SA_ALPHABET * 4u);
             }
             __syncwarp();
         }
         // ---- scores of this warp's 256 offsets for both sequences
+        uint32_t P[kR + 1];
+        to_prefixes_u16x2(D, P8, P);
         const int vb = (int)rows * vmin;
         unsigned long long keyA = 0ull, keyB = 0ull;
 #pragma unroll
@@ -1171,6 +1211,8 @@ int sa_cuda_solve_blob(const void* d_blob, const sa_blob_header* h, int32_t* d_o
     p.s2_cap = (h->max_rows_padded + 15u) & ~15u;
     p.win_cap = (h->max_window_bytes + 15u) & ~15u;
     p.write_empty = 1;
+    static const bool env_timeline = std::getenv("SA_TIMELINE") != nullptr;  // debug: phase timestamps in the control words
+    p.timeline = env_timeline ? 1u : 0u;
     if (h->flags & SA_FLAG_STREAM_MODE) {
         const uint32_t smem = 2u * kLutBytes + ((h->len1_padded + 15u) & ~15u) +
                               (uint32_t)kWarps * SA_STREAM_ROW_BLOCK * SA_ALPHABET * 4u + 64u;

@@ -119,7 +119,8 @@ size_t sa_format(const int32_t* results, int32_t nseq, char* buf, size_t cap);
 #define SA_DIAG_PER_WARP 256      /* 32 * R                                     */
 #define SA_ROW_UNROLL 8           /* U: rows per inner-loop trip                */
 #define SA_BLOB_MAGIC 0x31424153u /* "SAB1" */
-#define SA_BLOB_VERSION 2u
+#define SA_BLOB_VERSION 3u
+#define SA_PLAN_SMS 148u          /* SMs per GPU the planner balances for (B200)       */
 #define SA_SEQ1_TAIL_PAD 4608u    /* zero bytes after Seq1 so every window is in range */
 
 #define SA_MAX_WORLD 16
@@ -156,10 +157,10 @@ typedef struct sa_blob_header {
     uint32_t off_seq1;   /* uint8[len1_padded]: code*4 (pre-scaled LUT byte offset) */
     uint32_t off_seqtab; /* sa_seq_desc[nseq]                                       */
     uint32_t off_items;  /* sa_item[nitems], grouped by rank, costliest first       */
-    uint32_t off_seq2;   /* uint8 codes, each sequence 16-byte aligned, zero padded */
+    uint32_t off_seq2;   /* uint8 codes, grouped by rank, each sequence 16-byte aligned, zero padded */
     uint32_t max_rows_padded;  /* largest padded row count of any sequence          */
     uint32_t max_window_bytes; /* largest Seq1 window any item stages (16-B multiple) */
-    uint32_t chunk_bytes; /* fabric broadcast granularity */
+    uint32_t chunk_bytes; /* fabric staging granularity (one ready flag per chunk)  */
     uint32_t nchunks;
     uint32_t pad0;
     uint64_t total_cells;  /* sum over sequences of candidates                 */
@@ -168,11 +169,19 @@ typedef struct sa_blob_header {
     uint32_t rank_first_item[SA_MAX_WORLD + 1]; /* rank r owns items [r], [r+1]) */
     int32_t value_min;     /* min over {0, w1, -w2, -w3, -w4}: bias of the u16 pair lanes */
     uint32_t value_range;  /* max - min of the same set                               */
-    uint32_t off_pairs;    /* STREAM: sa_item[npairs] = (first, second or SA_NO_SEQ)  */
+    uint32_t off_pairs;    /* STREAM: sa_pair_rec[npairs], grouped by rank            */
     uint32_t npairs;
     uint32_t off_tile_items; /* TILE: sa_tile_item[nitems], same order as the item list */
-    uint32_t reserved[15];
-} sa_blob_header; /* 256 bytes */
+    /* ---- what each rank of a multi-GPU solve needs (the analogue of MPI_Bcast + MPI_Scatter,
+     * main.c:149-152,174): everyone the shared part [0, off_shared_end) = header + table + Seq1,
+     * rank r its slice of the item list, of the pair / tile-item records, and the letters of the
+     * sequences it scores, [rank_seq2_lo[r], rank_seq2_hi[r]). */
+    uint32_t off_shared_end;
+    uint32_t rank_first_pair[SA_MAX_WORLD + 1];
+    uint32_t rank_seq2_lo[SA_MAX_WORLD];
+    uint32_t rank_seq2_hi[SA_MAX_WORLD];
+    uint32_t reserved[157];
+} sa_blob_header; /* 1024 bytes */
 
 typedef struct sa_seq_desc {
     uint32_t off;      /* byte offset of the sequence's codes inside the blob  */
@@ -195,6 +204,19 @@ typedef struct sa_tile_item {
     uint8_t wd_log2, home;
     uint32_t pad[2];
 } sa_tile_item; /* 32 bytes */
+
+/* STREAM mode: one self-contained record per pair of sequences scored as u16x2 lanes (what
+ * sa_tile_item is for TILE mode): a warp needs the item and this record, nothing else. */
+typedef struct sa_pair_rec {
+    uint32_t a, b;         /* sequence indices (= result rows); b == SA_NO_SEQ: unpaired   */
+    uint32_t off_a, off_b; /* blob offsets of the two sequences' codes                     */
+    uint16_t len_a, len_b;
+    uint16_t crow;         /* rows every tile of the pair walks (multiple of 32)           */
+    uint16_t ntiles;
+    uint8_t home;          /* rank holding the pair's keys + arrival counter               */
+    uint8_t pad8[3];
+    uint32_t pad;
+} sa_pair_rec; /* 32 bytes */
 
 typedef struct sa_item {
     uint32_t seq;  /* TILE: sequence          PAIR: first sequence     STREAM: pair index    */
