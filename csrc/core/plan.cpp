@@ -115,6 +115,8 @@ extern "C" {
 // SA_MODE_TILE otherwise. Forcing SA_MODE_PAIR on an input outside its limits is an error.
 int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_t cap, size_t* blob_bytes) {
     using namespace sa;
+    const bool split_flag = (mode & SA_MODE_SPLIT_TILES) != 0;
+    mode &= ~SA_MODE_SPLIT_TILES;
     if (!p || !blob_bytes || world < 1 || world > SA_MAX_WORLD || mode < SA_MODE_AUTO || mode > SA_MODE_STREAM) {
         set_error("sa_plan_pack: bad argument");
         return SA_ERR_ARG;
@@ -336,62 +338,43 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     }
     const uint32_t nitems = (uint32_t)nitems64;
 
-    // ---- layout
-    uint32_t len1_padded = round_up(len1 + SA_SEQ1_TAIL_PAD, 16);
-    if (use_pairs) len1_padded = std::max(len1_padded, round_up(pair_cols_needed + 16u, 16));
-    uint64_t off = sizeof(sa_blob_header);
-    const uint32_t off_lut = (uint32_t)off;
-    off += sizeof(int32_t) * SA_ALPHABET * SA_ALPHABET;
-    const uint32_t off_seq1 = (uint32_t)off;
-    off += len1_padded;
-    const uint32_t off_seqtab = (uint32_t)off;
-    off += (uint64_t)sizeof(sa_seq_desc) * nseq;
-    off = (off + 15) / 16 * 16;
-    const uint32_t off_items = (uint32_t)off;
-    off += (uint64_t)sizeof(sa_item) * nitems;
-    off = (off + 15) / 16 * 16;
-    const uint32_t off_pairs = (uint32_t)off;
-    if (use_stream) off += (uint64_t)sizeof(sa_item) * pairs.size();
-    off = (off + 15) / 16 * 16;
-    const uint32_t off_tile_items = (uint32_t)off;
-    if (!use_pairs) off += (uint64_t)sizeof(sa_tile_item) * nitems;
-    off = (off + 31) / 32 * 32;
-    const uint32_t off_seq2 = (uint32_t)off;
-    std::vector<uint32_t> seq_off(nseq);
-    for (uint32_t s = 0; s < nseq; ++s) {
-        seq_off[s] = (uint32_t)off;
-        off += round_up(std::max(plans[s].rows_padded(), (uint32_t)p->seq2[s].size()), 16);
-        if (off >= 0xFFFFF000ull) {
-            set_error("blob larger than 4 GiB");
-            return SA_ERR_UNSUPPORTED;
-        }
-    }
-    const size_t total = (size_t)off;
-    *blob_bytes = total;
-    if (!dst) return SA_OK;
-    if (cap < total) {
-        set_error("sa_plan_pack_into: destination too small");
-        return SA_ERR_SMALL_BUFFER;
-    }
-
     // ---- partition: deal sequences (or tiles, when sequences are scarce) to ranks
     struct RankItem {
         uint32_t seq, tile;
     };
     std::vector<std::vector<RankItem>> per_rank((size_t)world);
     std::vector<uint8_t> home(nseq, 0);
+    std::vector<uint32_t> rank_first_pair(SA_MAX_WORLD + 1, 0);
+    bool by_tile = false;  // tiles of one sequence dealt to different ranks (cross-GPU argmax reduce)
+    // SA_SPLIT_TILES=1 forces the per-tile deal (tests and the strong-scaling benchmark line)
+    static const bool split_env = [] { const char* e = std::getenv("SA_SPLIT_TILES"); return e && *e && *e != '0'; }();
     if (use_pairs) {
         std::stable_sort(pairs.begin(), pairs.end(), [](const Pair& x, const Pair& y) { return x.g.item_cost > y.g.item_cost; });
         if (use_stream) {
             // whole pairs are dealt to the least-loaded rank, costliest first: every atomic stays local
             std::vector<uint64_t> load((size_t)world, 0);
+            std::vector<uint8_t> pair_rank(pairs.size(), 0);
             for (uint32_t pid = 0; pid < pairs.size(); ++pid) {
                 const int r = (int)(std::min_element(load.begin(), load.end()) - load.begin());
+                pair_rank[pid] = (uint8_t)r;
                 home[pairs[pid].a] = (uint8_t)r;
                 if (pairs[pid].b != SA_NO_SEQ) home[pairs[pid].b] = (uint8_t)r;
-                for (uint32_t t = 0; t < pairs[pid].g.ntiles; ++t) per_rank[(size_t)r].push_back({pid, t});
                 load[(size_t)r] += pairs[pid].g.item_cost * pairs[pid].g.ntiles;
             }
+            // renumber so that a rank's pairs are contiguous: a rank then needs ONE slice of the record table
+            std::vector<Pair> grouped;
+            grouped.reserve(pairs.size());
+            for (int r = 0; r < world; ++r) {
+                rank_first_pair[(size_t)r] = (uint32_t)grouped.size();
+                for (uint32_t pid = 0; pid < pairs.size(); ++pid) {
+                    if (pair_rank[pid] != r) continue;
+                    const uint32_t nid = (uint32_t)grouped.size();
+                    grouped.push_back(pairs[pid]);
+                    for (uint32_t t = 0; t < pairs[pid].g.ntiles; ++t) per_rank[(size_t)r].push_back({nid, t});
+                }
+            }
+            pairs.swap(grouped);
+            for (size_t r = (size_t)world; r <= SA_MAX_WORLD; ++r) rank_first_pair[r] = (uint32_t)pairs.size();
         } else {
             for (const Pair& pr : pairs) per_rank[0].push_back({pr.a, pr.b});
         }
@@ -401,7 +384,7 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
         std::stable_sort(by_cost.begin(), by_cost.end(),
                          [&](uint32_t a, uint32_t b) { return plans[a].item_cost > plans[b].item_cost; });
         std::vector<uint64_t> load((size_t)world, 0);
-        const bool by_tile = world > 1 && nseq < 2u * (uint32_t)world;
+        by_tile = world > 1 && (nseq < 2u * (uint32_t)world || split_env || split_flag);
         auto lightest = [&]() { return (int)(std::min_element(load.begin(), load.end()) - load.begin()); };
         for (uint32_t s : by_cost) {
             const SeqPlan& sp = plans[s];
@@ -422,6 +405,73 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
         }
     }
 
+    // ---- layout
+    uint32_t len1_padded = round_up(len1 + SA_SEQ1_TAIL_PAD, 16);
+    if (use_pairs) len1_padded = std::max(len1_padded, round_up(pair_cols_needed + 16u, 16));
+    uint64_t off = sizeof(sa_blob_header);
+    const uint32_t off_lut = (uint32_t)off;
+    off += sizeof(int32_t) * SA_ALPHABET * SA_ALPHABET;
+    const uint32_t off_seq1 = (uint32_t)off;
+    off += len1_padded;
+    const uint32_t off_seqtab = (uint32_t)off;
+    off += (uint64_t)sizeof(sa_seq_desc) * nseq;
+    off = (off + 15) / 16 * 16;
+    const uint32_t off_items = (uint32_t)off;
+    off += (uint64_t)sizeof(sa_item) * nitems;
+    off = (off + 15) / 16 * 16;
+    const uint32_t off_pairs = (uint32_t)off;
+    if (use_stream) off += (uint64_t)sizeof(sa_pair_rec) * pairs.size();
+    off = (off + 15) / 16 * 16;
+    const uint32_t off_tile_items = (uint32_t)off;
+    if (!use_pairs) off += (uint64_t)sizeof(sa_tile_item) * nitems;
+    off = (off + 31) / 32 * 32;
+    const uint32_t off_seq2 = (uint32_t)off;
+    // Seq2 letters grouped by the rank that scores them, so that a rank's share is ONE byte range it can
+    // pull from rank 0 (the MPI_Scatter of main.c:174). With tiles of one sequence dealt to several
+    // ranks (by_tile: few sequences) every rank needs every sequence: one group, every range = all.
+    std::vector<uint32_t> seq_off(nseq);
+    std::vector<uint32_t> seq2_lo((size_t)world, 0), seq2_hi((size_t)world, 0);
+    // Inside a rank's group the sequences follow the rank's item order (costliest first): the chunks a
+    // rank stages first are the ones its first items read.
+    std::vector<std::vector<uint32_t>> group((size_t)world);
+    {
+        std::vector<uint8_t> placed(nseq, 0);
+        for (int r = 0; r < world; ++r)
+            for (const RankItem& it : per_rank[(size_t)r]) {
+                uint32_t members[2] = {it.seq, SA_NO_SEQ};
+                if (use_stream) members[0] = pairs[it.seq].a, members[1] = pairs[it.seq].b;
+                else if (use_pairs) members[1] = it.tile;  // PAIR items are (first, second)
+                for (uint32_t s : members) {
+                    if (s == SA_NO_SEQ || placed[s]) continue;
+                    placed[s] = 1;
+                    group[by_tile ? 0u : (size_t)home[s]].push_back(s);
+                }
+            }
+        for (uint32_t s = 0; s < nseq; ++s)
+            if (!placed[s]) group[0].push_back(s);  // candidate-free sequences: never read by a kernel
+    }
+    for (int r = 0; r < world; ++r) {
+        seq2_lo[(size_t)r] = (uint32_t)off;
+        for (uint32_t s : group[(size_t)r]) {
+            seq_off[s] = (uint32_t)off;
+            off += round_up(std::max(plans[s].rows_padded(), (uint32_t)p->seq2[s].size()), 16);
+            if (off >= 0xFFFFF000ull) {
+                set_error("blob larger than 4 GiB");
+                return SA_ERR_UNSUPPORTED;
+            }
+        }
+        seq2_hi[(size_t)r] = (uint32_t)off;
+    }
+    if (by_tile)
+        for (int r = 0; r < world; ++r) seq2_lo[(size_t)r] = off_seq2, seq2_hi[(size_t)r] = (uint32_t)off;
+    const size_t total = (size_t)off;
+    *blob_bytes = total;
+    if (!dst) return SA_OK;
+    if (cap < total) {
+        set_error("sa_plan_pack_into: destination too small");
+        return SA_ERR_SMALL_BUFFER;
+    }
+
     // ---- fill
     unsigned char* base = static_cast<unsigned char*>(dst);
     std::memset(base, 0, off_seq2);  // header + tables + Seq1; every Seq2 slot zeroes its own padding below
@@ -432,10 +482,6 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     h->flags = use_stream ? SA_FLAG_STREAM_MODE : (use_pairs ? SA_FLAG_PAIR_MODE : 0u);
     h->off_pairs = use_stream ? off_pairs : 0u;
     h->npairs = use_stream ? (uint32_t)pairs.size() : 0u;
-    if (use_stream) {
-        sa_item* pt = reinterpret_cast<sa_item*>(base + off_pairs);
-        for (uint32_t pid = 0; pid < pairs.size(); ++pid) pt[pid] = sa_item{pairs[pid].a, pairs[pid].b};
-    }
     std::memcpy(h->weights, p->weights, sizeof(h->weights));
     h->len1 = len1;
     h->len1_padded = len1_padded;
@@ -448,8 +494,8 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     h->off_seq2 = off_seq2;
     h->max_rows_padded = max_rows;
     h->max_window_bytes = max_window;
-    // fabric broadcast granularity: 8 KiB (so that even a 30 KB blob is pushed by several CTAs
-    // at once), grown so that a blob never needs more flags than exist
+    // fabric staging granularity: 8 KiB (one ready flag per chunk, one chunk per copy item: even a
+    // 30 KB problem is pulled by several CTAs at once), grown so that a blob never needs more flags than exist
     h->chunk_bytes = std::max<uint32_t>(1u << 13, round_up((uint32_t)((total + SA_FABRIC_MAX_CHUNKS - 1) / SA_FABRIC_MAX_CHUNKS), 1u << 13));
     h->nchunks = (uint32_t)((total + h->chunk_bytes - 1) / h->chunk_bytes);
     h->total_cells = total_cells;
@@ -488,7 +534,7 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
                     bad |= c;
                     dstq[i] = (unsigned char)c;
                 }
-                const size_t slot = (s + 1 < nseq ? seq_off[s + 1] : total) - seq_off[s];
+                const size_t slot = round_up(std::max(sp.rows_padded(), (uint32_t)q.size()), 16);
                 std::memset(dstq + q.size(), 0, slot - q.size());
             }
             if (bad < 0) unknown_byte.store(1);
@@ -508,6 +554,29 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
         for (const RankItem& it : per_rank[(size_t)r]) items[w++] = sa_item{it.seq, it.tile};
     }
     for (int r = world; r <= SA_MAX_WORLD; ++r) h->rank_first_item[r] = w;
+    h->off_shared_end = off_seqtab;
+    for (int r = 0; r <= SA_MAX_WORLD; ++r) h->rank_first_pair[r] = use_stream ? rank_first_pair[(size_t)r] : 0u;
+    for (int r = 0; r < SA_MAX_WORLD; ++r) {
+        h->rank_seq2_lo[r] = r < world ? seq2_lo[(size_t)r] : (uint32_t)total;
+        h->rank_seq2_hi[r] = r < world ? seq2_hi[(size_t)r] : (uint32_t)total;
+    }
+    if (use_stream) {
+        sa_pair_rec* pt = reinterpret_cast<sa_pair_rec*>(base + off_pairs);
+        for (uint32_t pid = 0; pid < pairs.size(); ++pid) {
+            const Pair& pr = pairs[pid];
+            sa_pair_rec rec{};
+            rec.a = pr.a;
+            rec.b = pr.b;
+            rec.off_a = tab[pr.a].off;
+            rec.len_a = tab[pr.a].len;
+            rec.off_b = pr.b == SA_NO_SEQ ? rec.off_a : tab[pr.b].off;
+            rec.len_b = pr.b == SA_NO_SEQ ? rec.len_a : tab[pr.b].len;
+            rec.crow = (uint16_t)pr.g.crow;
+            rec.ntiles = (uint16_t)pr.g.ntiles;
+            rec.home = tab[pr.a].home;
+            pt[pid] = rec;
+        }
+    }
     h->off_tile_items = use_pairs ? 0u : off_tile_items;
     if (!use_pairs) {
         sa_tile_item* fat = reinterpret_cast<sa_tile_item*>(base + off_tile_items);
@@ -600,11 +669,28 @@ int score_pair_cpu(const BlobView& b, uint32_t it, uint64_t* keys) {
     // PAIR: the item is the pair, all its tiles, 16 warps = wd x wr.
     // STREAM: the item is (pair, one tile), a single warp walks all rows (wd = wr = 1).
     const bool stream = (b.h->flags & SA_FLAG_STREAM_MODE) != 0;
-    const sa_item* pairs = reinterpret_cast<const sa_item*>(b.base + b.h->off_pairs);
-    const uint32_t ia = stream ? pairs[b.items[it].seq].seq : b.items[it].seq;
-    const uint32_t ib = stream ? pairs[b.items[it].seq].tile : b.items[it].tile;
-    const sa_seq_desc& da = b.tab[ia];
-    const sa_seq_desc* db = ib == SA_NO_SEQ ? nullptr : &b.tab[ib];
+    const sa_pair_rec* pairs = reinterpret_cast<const sa_pair_rec*>(b.base + b.h->off_pairs);
+    const uint32_t ia = stream ? pairs[b.items[it].seq].a : b.items[it].seq;
+    const uint32_t ib = stream ? pairs[b.items[it].seq].b : b.items[it].tile;
+    // STREAM: the kernel reads only the self-contained pair record, and so does this walk (a rank of a
+    // multi-GPU solve holds no sequence table); where the table IS present the two must agree.
+    sa_seq_desc da_rec{}, db_rec{};
+    if (stream) {
+        const sa_pair_rec& pr = pairs[b.items[it].seq];
+        const sa_seq_desc& ta = b.tab[pr.a];
+        const bool have_tab = ta.off != 0u;
+        const bool ok_b = pr.b == SA_NO_SEQ || !have_tab || (pr.off_b == b.tab[pr.b].off && pr.len_b == b.tab[pr.b].len);
+        if (have_tab && (pr.off_a != ta.off || pr.len_a != ta.len || pr.crow != ta.crow || pr.ntiles != ta.ntiles || pr.home != ta.home || !ok_b)) {
+            set_error("pair walk: pair record disagrees with the sequence table");
+            return SA_ERR_ARG;
+        }
+        da_rec.off = pr.off_a, da_rec.len = pr.len_a, da_rec.crow = pr.crow, da_rec.ntiles = pr.ntiles, da_rec.home = pr.home;
+        da_rec.ndiag = (int32_t)b.h->len1 - (int32_t)pr.len_a;
+        db_rec = da_rec;
+        db_rec.off = pr.off_b, db_rec.len = pr.len_b, db_rec.ndiag = (int32_t)b.h->len1 - (int32_t)pr.len_b;
+    }
+    const sa_seq_desc& da = stream ? da_rec : b.tab[ia];
+    const sa_seq_desc* db = ib == SA_NO_SEQ ? nullptr : (stream ? &db_rec : &b.tab[ib]);
     const uint32_t nwarps = stream ? 1u : kWarps;
     const uint32_t wd = 1u << da.wd_log2, wr = nwarps / wd, crow = da.crow, rows = crow * wr;
     const uint32_t tile_begin = stream ? b.items[it].tile : 0u, tile_end = stream ? tile_begin + 1u : da.ntiles;
@@ -715,14 +801,18 @@ int sa_blob_score_items_cpu(const void* blob, size_t blob_bytes, uint32_t first_
     const sa_tile_item* fat = reinterpret_cast<const sa_tile_item*>(b.base + b.h->off_tile_items);
     for (uint32_t it = first_item; it < last_item; ++it) {
         const uint32_t s = b.items[it].seq, tile = b.items[it].tile;
-        const sa_seq_desc& sd = b.tab[s];
-        // the kernel reads the self-contained record; it must say what the two tables say
-        if (fat[it].seq != s || fat[it].tile != tile || fat[it].off != sd.off || fat[it].ndiag != sd.ndiag ||
-            fat[it].len != sd.len || fat[it].crow != sd.crow || fat[it].ntiles != sd.ntiles ||
-            fat[it].wd_log2 != sd.wd_log2 || fat[it].home != sd.home) {
+        // the kernel reads only the self-contained record, and so does this walk; where the sequence
+        // table is present (it is not on a rank that pulled just its own share) the two must agree
+        const sa_seq_desc& tabd = b.tab[s];
+        if (fat[it].seq != s || fat[it].tile != tile ||
+            (tabd.off != 0u && (fat[it].off != tabd.off || fat[it].ndiag != tabd.ndiag || fat[it].len != tabd.len || fat[it].crow != tabd.crow ||
+                                fat[it].ntiles != tabd.ntiles || fat[it].wd_log2 != tabd.wd_log2 || fat[it].home != tabd.home))) {
             set_error("sa_blob_score_items_cpu: tile item record disagrees with the item list / sequence table");
             return SA_ERR_ARG;
         }
+        sa_seq_desc sd{};
+        sd.off = fat[it].off, sd.len = fat[it].len, sd.crow = fat[it].crow, sd.ndiag = fat[it].ndiag;
+        sd.ntiles = fat[it].ntiles, sd.wd_log2 = fat[it].wd_log2, sd.home = fat[it].home;
         const unsigned char* s2 = b.base + sd.off;
         const uint32_t wd = 1u << sd.wd_log2, wr = kWarps / wd, crow = sd.crow;
         const uint32_t tn = kWarpDiag * wd, n0 = tile * tn;
@@ -769,6 +859,23 @@ int sa_blob_score_items_cpu(const void* blob, size_t blob_bytes, uint32_t first_
         }
         keys[s] = std::max(keys[s], tile_key);
     }
+    return SA_OK;
+}
+
+int sa_blob_rank_ranges(const sa_blob_header* h, uint32_t rank, uint32_t lo[4], uint32_t hi[4]) {
+    if (!h || !lo || !hi || h->magic != SA_BLOB_MAGIC || h->version != SA_BLOB_VERSION || rank >= h->world) {
+        sa::set_error("sa_blob_rank_ranges: bad argument");
+        return SA_ERR_ARG;
+    }
+    const bool stream = (h->flags & SA_FLAG_STREAM_MODE) != 0;
+    const uint32_t i0 = h->rank_first_item[rank], i1 = h->rank_first_item[rank + 1];
+    lo[0] = 0, hi[0] = h->off_shared_end;
+    lo[1] = h->off_items + 8u * i0, hi[1] = h->off_items + 8u * i1;
+    if (stream) lo[2] = h->off_pairs + 32u * h->rank_first_pair[rank], hi[2] = h->off_pairs + 32u * h->rank_first_pair[rank + 1];
+    else lo[2] = h->off_tile_items + 32u * i0, hi[2] = h->off_tile_items + 32u * i1;
+    lo[3] = h->rank_seq2_lo[rank], hi[3] = h->rank_seq2_hi[rank];
+    if (i1 <= i0)
+        for (int i = 0; i < 4; ++i) lo[i] = hi[i] = 0;  // a rank without items needs nothing
     return SA_OK;
 }
 

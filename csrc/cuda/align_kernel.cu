@@ -29,6 +29,7 @@
 #include <new>
 #include <string>
 
+#include "ptx_helpers.cuh"
 #include "seqalign.h"
 
 namespace {
@@ -57,91 +58,24 @@ struct KParams {
     uint32_t rank, world, epoch, use_mc;
     unsigned char* peer[SA_MAX_WORLD];  // every rank's symmetric buffer as mapped into this process
     unsigned char* mc;                  // NVLS multicast alias of the same buffer, or null
-    uint32_t off_ctrl, off_key, off_cnt, off_out, off_blob;
+    uint32_t off_ctrl, off_hdr_ll, off_key, off_cnt, off_out, off_out_ll, off_blob;
     unsigned long long timeout_ns;
     uint32_t timeline;  // 1: record the globaltimer timeline in the control block
-    uint32_t skip_push; // 1: re-solve of the blob the peers already hold (debug / resident re-solve)
+    uint32_t skip_push; // 1: re-solve of the blob every rank already holds (resident re-solve)
 };
 
-// Words of the control block at the start of every rank's symmetric buffer.
-constexpr uint32_t kCtlNext = 0, kCtlCtasDone = 1, kCtlRanksDone = 2, kCtlError = 3, kCtlAllHere = 4, kCtlPushed = 5, kCtlFlags = 64;
+// Words of the control block at the start of every rank's symmetric buffer (all local to the rank
+// that owns the buffer: nothing in here is written by another GPU).
+constexpr uint32_t kCtlNext = 0, kCtlCtasDone = 1, kCtlSharedNext = 2, kCtlError = 3, kCtlAllHere = 4, kCtlCopied = 5, kCtlFlags = 64;
 constexpr uint32_t kMaxChunks = SA_FABRIC_MAX_CHUNKS;
-// Optional timeline (globaltimer ns) in control words 16..31 as five 64-bit slots:
-// 0 earliest CTA start, 1 prefix ready (latest), 2 last item finished, 3 arrival sent, 4 all arrived,
-// 5 first sight of the "whole blob is here" flag, 6 items that had to wait for chunk flags, 7 ns spent so.
+constexpr uint32_t kHdrWords = sizeof(sa_blob_header) / 4;
+// Optional timeline (globaltimer ns) in control words 16..63 as 64-bit slots:
+// 0 earliest CTA start, 1 header known (latest CTA), 2 last item finished, 4 every result row validated (rank 0),
+// 5 all of this rank's chunks staged, 6 items that had to wait for a chunk, 7 ns spent so, 8..10 item-queue quartiles,
+// 11..15 latest CTA to reach each phase of its first item, 16 last CTA exit, 17 first copy item done.
 constexpr uint32_t kCtlTimes = 16;
 
-// ------------------------------------------------------------------ PTX helpers
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_fence_init() {
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(bar), "r"(parity)
-            : "memory");
-    } while (!done);
-}
-// TMA bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP).
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                 "l"(src), "r"(bytes), "r"(bar)
-                 : "memory");
-}
-
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
-    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
-// One store that the NVSwitch replicates into every GPU bound to the multicast object.
-__device__ __forceinline__ void multimem_st_v4(void* mc_addr, int4 v) {
-    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "r"(v.x), "r"(v.y),
-                 "r"(v.z), "r"(v.w)
-                 : "memory");
-}
-__device__ __forceinline__ unsigned long long global_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-// Bounded wait for a flag written by a peer GPU (never an unbounded spin: a dead peer must not
-// hang this GPU). Polls with relaxed loads — an acquire load per poll would
-// invalidate this SM's L1 every time — and the CALLER issues one acquire fence
-// (__threadfence_system) after its last flag. Returns false on timeout.
-__device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t epoch, unsigned long long timeout_ns) {
-    if ((int)(ld_relaxed_sys(flag) - epoch) >= 0) return true;
-    const unsigned long long t0 = global_ns();
-    for (;;) {
-        if ((int)(ld_relaxed_sys(flag) - epoch) >= 0) return true;
-        __nanosleep(64);
-        if (global_ns() - t0 > timeout_ns) return false;
-    }
-}
+using namespace sa_ptx;  // csrc/cuda/ptx_helpers.cuh
 
 __device__ __forceinline__ unsigned long long pack_key(int score, uint32_t n) {
     return ((unsigned long long)((uint32_t)score ^ 0x80000000u) << 32) | (unsigned long long)(0xFFFFFFFFu - n);
@@ -254,27 +188,126 @@ __device__ __forceinline__ int first_k_on_diagonal(const int* lut_i, const unsig
 
 // Shared by every fabric launch: set when one of this CTA's bounded cross-GPU waits timed out.
 __shared__ uint32_t s_abort;
-// Set once this CTA has observed rank 0's "whole blob has landed" flag: no more per-item waits.
+// Set once this CTA has seen that all of its rank's chunks are staged: no more per-item waits.
 __shared__ uint32_t s_all_here;
+// The blob header as every CTA of a fabric launch sees it: kernel parameter on rank 0, received
+// through the flag-in-data header packet on the others.
+__shared__ __align__(16) sa_blob_header s_hdr;
 
-// True when the caller may read the blob bytes [lo, hi) of a fabric launch on a rank other than 0.
+// ---- how the data moves in a multi-GPU solve (replaces main.c:149-152 Bcast x4, :174 Scatter, :195-197 Gather x3)
+//
+//  * Broadcast of what is shared. The 1 KB header (weights, sizes, the whole partition) travels as a
+//    "flag in data" packet: rank 0's first CTA stores, for every 32-bit header word, the 64-bit value
+//    (epoch << 32 | word) into EVERY rank's packet area — one multimem.st per word through the
+//    NVSwitch (or one store per peer without multicast). 8-byte stores are single-copy atomic, so a
+//    receiver that sees the epoch in the upper half has the word: no fence on the sender, no separate
+//    flag, one NVLink one-way trip (the packet also says "rank 0's kernel is running", i.e. its H2D
+//    copy is complete). The table and Seq1 follow by the pull below.
+//  * Scatter. Every rank other than 0 PULLS what it needs from rank 0's buffer into its own: the
+//    shared part [0, off_shared_end) and its own slices of the item list, the record table and the
+//    Seq2 letters (the header says where they are) — ingress per GPU is its own share, rank 0's SMs
+//    do not copy anything. The first items of the rank's work queue are these copies, one 8 KB chunk
+//    each (LDG.128 from the peer mapping -> STG.128 local -> gpu fence -> local chunk flag); scoring
+//    items follow and wait, per item, only for the chunks they read.
+//  * Gather. Whoever finishes a sequence stores its row straight into rank 0's table as two
+//    self-validating 8-byte words (score | epoch, n | k | epoch): no fence, no arrival counter. Rank 0's
+//    CTAs, once out of items, check every row's tags (bounded) and rewrite the row as
+//    (score, n, k, 0); rank 0's kernel completing therefore means the table is complete.
+//  * Reduce (a sequence whose tiles were dealt to several ranks): packed 64-bit (score, ~n) keys and
+//    the arrival counter live on the sequence's home rank; tiles fold in with atomicMax.sys /
+//    atomicAdd.sys over NVLink and the last arriver finishes the sequence.
+struct PullPlan {
+    uint32_t first[4], count[4], total;
+};
+__device__ __forceinline__ PullPlan make_pull_plan(const sa_blob_header& h, uint32_t rank) {
+    PullPlan pp;
+    const bool stream = (h.flags & SA_FLAG_STREAM_MODE) != 0u;
+    const uint32_t i0 = h.rank_first_item[rank], i1 = h.rank_first_item[rank + 1];
+    uint32_t lo[4], hi[4];
+    lo[0] = 0u, hi[0] = h.off_shared_end;
+    lo[1] = h.off_items + 8u * i0, hi[1] = h.off_items + 8u * i1;
+    if (stream) lo[2] = h.off_pairs + 32u * h.rank_first_pair[rank], hi[2] = h.off_pairs + 32u * h.rank_first_pair[rank + 1];
+    else lo[2] = h.off_tile_items + 32u * i0, hi[2] = h.off_tile_items + 32u * i1;
+    lo[3] = h.rank_seq2_lo[rank], hi[3] = h.rank_seq2_hi[rank];
+    const uint32_t cb = h.chunk_bytes;
+    int prev_last = -1;
+    pp.total = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        pp.first[i] = 0u, pp.count[i] = 0u;
+        if (i1 <= i0 || hi[i] <= lo[i]) continue;  // a rank without items stages nothing
+        int f = (int)(lo[i] / cb);
+        const int l = (int)((hi[i] - 1u) / cb);
+        if (f <= prev_last) f = prev_last + 1;  // the boundary chunk of the previous range is already on the list
+        if (l >= f) pp.first[i] = (uint32_t)f, pp.count[i] = (uint32_t)(l - f + 1);
+        if (l > prev_last) prev_last = l;
+        pp.total += pp.count[i];
+    }
+    return pp;
+}
+__device__ __forceinline__ uint32_t pull_chunk_of(const PullPlan& pp, uint32_t j) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (j < pp.count[i]) return pp.first[i] + j;
+        j -= pp.count[i];
+    }
+    return 0u;
+}
+
+// Copy item `j` of this rank: stage one chunk of rank 0's blob locally. `t`/`nt`: this thread's index and
+// the number of threads cooperating (a CTA in TILE mode, a warp in STREAM mode). The caller synchronises
+// the cooperating threads afterwards and lets ONE of them call pull_publish.
+__device__ __forceinline__ void pull_copy(const KParams& p, const sa_blob_header& h, uint32_t chunk, uint32_t t, uint32_t nt) {
+    const uint32_t cb = h.chunk_bytes, base = chunk * cb;
+    const uint32_t n16 = (min(cb, h.total_bytes - base) + 15u) >> 4;
+    const int4* src = reinterpret_cast<const int4*>(p.peer[0] + p.off_blob + base);
+    int4* dst = reinterpret_cast<int4*>(p.peer[p.rank] + p.off_blob + base);
+    uint32_t i = t;
+    for (; i + 3u * nt < n16; i += 4u * nt) {  // four loads in flight per thread: an NVLink read is ~2 us away
+        const int4 a = src[i], b = src[i + nt], c = src[i + 2u * nt], d = src[i + 3u * nt];
+        dst[i] = a, dst[i + nt] = b, dst[i + 2u * nt] = c, dst[i + 3u * nt] = d;
+    }
+    for (; i < n16; i += nt) dst[i] = src[i];
+}
+__device__ __forceinline__ void pull_publish(const KParams& p, uint32_t* my_ctl, uint32_t chunk, uint32_t n_copy) {
+    unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
+    __threadfence();  // the cooperating threads' stores (ordered before this by their barrier) are visible GPU-wide
+    st_relaxed_gpu(my_ctl + kCtlFlags + chunk, p.epoch);
+    if (p.timeline) atomicMin(&times[17], global_ns());
+    if (atomicAdd(&my_ctl[kCtlCopied], 1u) + 1u == n_copy) {  // every pusher fenced before it counted itself
+        my_ctl[kCtlCopied] = 0u;
+        st_relaxed_gpu(my_ctl + kCtlAllHere, p.epoch);
+        if (p.timeline) times[5] = global_ns();
+    }
+}
+
+// Bounded wait for a LOCAL flag raised by another CTA of this GPU (relaxed polls, one fence by the caller).
+__device__ __forceinline__ bool wait_local_flag(const uint32_t* flag, uint32_t epoch, unsigned long long timeout_ns) {
+    if ((int)(ld_relaxed_gpu(flag) - epoch) >= 0) return true;
+    const unsigned long long t0 = global_ns();
+    for (;;) {
+        if ((int)(ld_relaxed_gpu(flag) - epoch) >= 0) return true;
+        __nanosleep(32);
+        if (global_ns() - t0 > timeout_ns) return false;
+    }
+}
+
+// True when the blob bytes [lo, hi) are staged in this rank's buffer (always, on rank 0).
 // Fast path: the cached / single "all here" flag. Slow path: the flags of the covering chunks.
-__device__ __forceinline__ bool fabric_bytes_ready(const KParams& p, const sa_blob_header* hdr, uint32_t* my_ctl,
-                                                   uint32_t lo, uint32_t hi) {
+__device__ __forceinline__ bool fabric_bytes_ready(const KParams& p, uint32_t* my_ctl, uint32_t lo, uint32_t hi) {
     volatile uint32_t* const cached = &s_all_here;
     if (*cached) return true;
     unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
-    if ((int)(ld_relaxed_sys(my_ctl + kCtlAllHere) - p.epoch) >= 0) {
-        __threadfence_system();  // acquire: everything published before the flag is visible from here on
+    if ((int)(ld_relaxed_gpu(my_ctl + kCtlAllHere) - p.epoch) >= 0) {
+        __threadfence();  // acquire: everything staged before the flag is visible from here on
         *cached = 1u;
-        if (p.timeline) atomicMin(&times[5], global_ns());
         return true;
     }
     const unsigned long long t0 = p.timeline ? global_ns() : 0ull;
-    const uint32_t cb = hdr->chunk_bytes;
+    const uint32_t cb = s_hdr.chunk_bytes;
     for (uint32_t c = lo / cb; c <= (hi - 1u) / cb; ++c)
-        if (!wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns)) return false;
-    __threadfence_system();  // one acquire fence for all the chunk flags just observed
+        if (!wait_local_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns)) return false;
+    __threadfence();  // one acquire fence for all the chunk flags just observed
     if (p.timeline) {
         atomicAdd(&times[6], 1ull);
         atomicAdd(&times[7], global_ns() - t0);
@@ -282,124 +315,120 @@ __device__ __forceinline__ bool fabric_bytes_ready(const KParams& p, const sa_bl
     return true;
 }
 
-// Fabric prologue, once per CTA (requires a preceding __syncthreads after s_abort = 0):
-// rank 0 pushes its share of the blob's chunks to every peer and publishes their flags; the other
-// ranks wait until the chunks holding header, table, Seq1, descriptors and items have landed.
-__device__ __forceinline__ void fabric_prologue(const KParams& p) {
-    constexpr bool kFabric = true;
+// Fabric prologue, once per CTA (requires a preceding __syncthreads after s_abort = 0): rank 0 sends the
+// header packet (its first CTA only) and takes the header from its kernel parameter; every other rank
+// receives it. On return s_hdr is valid in every CTA, or s_abort is set.
+__device__ __forceinline__ void fabric_prologue(const KParams& p, const sa_blob_header& hdr0) {
     const uint32_t tid = threadIdx.x;
-    const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
     uint32_t* const my_ctl = reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl);
-    if (kFabric && p.world > 1) {
-        if (p.rank == 0 && p.skip_push) {
-            // the peers still hold this blob from the previous launch (same epoch): nothing to send
-        } else if (p.rank == 0) {
-            // ---- broadcast, fused with scoring: each CTA pushes its share of chunks, then scores
-            const uint32_t total = hdr->total_bytes, chunk = hdr->chunk_bytes, nchunks = hdr->nchunks;
-            for (uint32_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
-                const uint32_t base = c * chunk;
-                const uint32_t n16 = (min(chunk, total - base) + 15u) >> 4;
-                const int4* src = reinterpret_cast<const int4*>(p.blob + base);
+    uint32_t* const dst = reinterpret_cast<uint32_t*>(&s_hdr);
+    if (p.rank == 0) {
+        const uint32_t* const src = reinterpret_cast<const uint32_t*>(&hdr0);
+        if (tid < kHdrWords) {
+            const uint32_t w = src[tid];
+            dst[tid] = w;
+            if (blockIdx.x == 0 && p.world > 1 && !p.skip_push) {
+                const unsigned long long pkt = ((unsigned long long)p.epoch << 32) | w;
                 if (p.use_mc) {
-                    int4* dst = reinterpret_cast<int4*>(p.mc + p.off_blob + base);
-                    for (uint32_t i = tid; i < n16; i += kThreads) multimem_st_v4(dst + i, src[i]);
+                    multimem_st_u64(p.mc + p.off_hdr_ll + 8u * tid, pkt);
                 } else {
-                    for (uint32_t i = tid; i < n16; i += kThreads) {
-                        const int4 v = src[i];
-                        for (uint32_t r = 1; r < p.world; ++r)
-                            reinterpret_cast<int4*>(p.peer[r] + p.off_blob + base)[i] = v;
-                    }
-                }
-                __syncthreads();
-                if (tid == 0) {
-                    // ONE system fence (cumulative over the CTA's stores ordered before it by the barrier),
-                    // then relaxed flag stores: a st.release per peer would repeat the fence world-1 times
-                    // (measured: 33 us to publish 19 chunks to 7 peers, profiles/fabric/timeline_8gpu_*).
-                    __threadfence_system();
                     for (uint32_t r = 1; r < p.world; ++r)
-                        st_relaxed_sys(reinterpret_cast<uint32_t*>(p.peer[r] + p.off_ctrl) + kCtlFlags + c, p.epoch);
-                    // The CTA that publishes the last chunk also raises one "everything is here" flag, so
-                    // that peers stop polling (and stop invalidating their L1) per item once the broadcast
-                    // is over. Every pusher fenced at system scope before it counted itself.
-                    if (atomicAdd(&my_ctl[kCtlPushed], 1u) + 1u == nchunks) {
-                        my_ctl[kCtlPushed] = 0u;
-                        for (uint32_t r = 1; r < p.world; ++r)
-                            st_relaxed_sys(reinterpret_cast<uint32_t*>(p.peer[r] + p.off_ctrl) + kCtlAllHere, p.epoch);
+                        st_relaxed_sys_u64(reinterpret_cast<unsigned long long*>(p.peer[r] + p.off_hdr_ll) + tid, pkt);
+                }
+            }
+        }
+    } else {
+        const unsigned long long* const pkt = reinterpret_cast<const unsigned long long*>(p.peer[p.rank] + p.off_hdr_ll) + tid;
+        if (tid < kHdrWords) {
+            unsigned long long v = ld_relaxed_sys_u64(pkt);
+            if ((uint32_t)(v >> 32) != p.epoch) {
+                const unsigned long long t0 = global_ns();
+                for (;;) {
+                    v = ld_relaxed_sys_u64(pkt);
+                    if ((uint32_t)(v >> 32) == p.epoch) break;
+                    __nanosleep(32);
+                    if (global_ns() - t0 > p.timeout_ns) {
+                        s_abort = 1u;
+                        atomicExch(my_ctl + kCtlError, 1u);
+                        break;
                     }
                 }
             }
-        } else {
-            // ---- wait for the chunks that hold header, table, Seq1, descriptors and items
-            if (tid == 0) {
-                bool ok = wait_flag(my_ctl + kCtlFlags, p.epoch, p.timeout_ns);
-                if (ok) {
-                    __threadfence_system();  // the header must be read after its chunk's flag
-                    const uint32_t npre = (hdr->off_seq2 + hdr->chunk_bytes - 1u) / hdr->chunk_bytes;
-                    for (uint32_t c = 1; ok && c < npre; ++c) ok = wait_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns);
-                }
-                if (!ok) {
-                    s_abort = 1u;
-                    atomicExch(my_ctl + kCtlError, 1u);
-                }
-                __threadfence_system();  // acquire side of the flags polled with relaxed loads
-                fence_proxy_async();
-            }
-            __syncthreads();
+            dst[tid] = (uint32_t)v;
         }
+    }
+    __syncthreads();
+    if (p.rank != 0 && s_abort == 0u && (s_hdr.magic != SA_BLOB_MAGIC || s_hdr.world != p.world)) {  // never walk a header that is not one
+        if (tid == 0) {
+            s_abort = 1u;
+            atomicExch(my_ctl + kCtlError, 3u);
+        }
+        __syncthreads();
+    }
+    if (tid == 0 && (p.rank == 0 || p.skip_push)) s_all_here = 1u;  // nothing to stage
+    __syncthreads();
+}
+
+// A finished sequence's row, stored into rank 0's table as two self-validating words.
+__device__ __forceinline__ void post_result(const KParams& p, uint32_t seq, int score, uint32_t n, uint32_t k) {
+    unsigned long long* const row = reinterpret_cast<unsigned long long*>(p.peer[0] + p.off_out_ll) + 2u * seq;
+    st_relaxed_sys_u64(row, ((unsigned long long)p.epoch << 32) | (uint32_t)score);
+    st_relaxed_sys_u64(row + 1, ((unsigned long long)(p.epoch & 0x7FFFFFFFu) << 33) | ((unsigned long long)(k & 0x1FFFu) << 20) | (n & 0xFFFFFu));
+}
+
+// Rank 0, once a CTA is out of items: validate a share of the result rows (bounded) and rewrite them in
+// the host's (score, n, k, 0) format. Rows of candidate-free sequences were written directly.
+__device__ __forceinline__ void collect_results(const KParams& p, uint32_t* my_ctl) {
+    const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + s_hdr.off_seqtab);
+    const unsigned long long* const ll = reinterpret_cast<const unsigned long long*>(p.peer[0] + p.off_out_ll);
+    int4* const out = reinterpret_cast<int4*>(p.peer[0] + p.off_out);
+    const unsigned long long tag1 = (unsigned long long)(p.epoch & 0x7FFFFFFFu);
+    for (uint32_t s = blockIdx.x * kThreads + threadIdx.x; s < s_hdr.nseq; s += gridDim.x * kThreads) {
+        if (seqtab[s].ntiles == 0) continue;
+        unsigned long long a = ld_relaxed_sys_u64(ll + 2u * s), b = ld_relaxed_sys_u64(ll + 2u * s + 1u);
+        if ((uint32_t)(a >> 32) != p.epoch || (b >> 33) != tag1) {
+            const unsigned long long t0 = global_ns();
+            for (;;) {
+                a = ld_relaxed_sys_u64(ll + 2u * s), b = ld_relaxed_sys_u64(ll + 2u * s + 1u);
+                if ((uint32_t)(a >> 32) == p.epoch && (b >> 33) == tag1) break;
+                __nanosleep(64);
+                if (global_ns() - t0 > p.timeout_ns) {
+                    atomicExch(my_ctl + kCtlError, 2u);
+                    return;
+                }
+            }
+        }
+        out[s] = make_int4((int)(uint32_t)a, (int)(b & 0xFFFFFu), (int)((b >> 20) & 0x1FFFu), 0);
     }
 }
 
-// Launch epilogue, once per CTA after its last item: the last CTA of the launch re-arms the work
-// queue; in a fabric launch it also tells rank 0 that this rank has delivered, and rank 0's last CTA
-// waits (bounded) for every rank.
+// Launch epilogue, once per CTA after its last item: the last CTA of the launch re-arms the work queue.
 template <bool kFabric>
 __device__ __forceinline__ void launch_epilogue(const KParams& p) {
     const uint32_t tid = threadIdx.x;
     uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
     unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
-    const bool timeline = kFabric && p.timeline != 0u;
-    // Last CTA out re-arms the work queue for the next launch.
+    if (kFabric && p.rank == 0 && s_abort == 0u) {
+        collect_results(p, my_ctl);
+        if (p.timeline && tid == 0) atomicMax(&times[4], global_ns());
+    }
     if (tid == 0) {
-        if (timeline) atomicMax(&times[2], global_ns());
-        if (kFabric) __threadfence_system(); else __threadfence();
+        __threadfence();
         const unsigned int done = atomicAdd(&my_ctl[kCtlCtasDone], 1u);
         if (done + 1u == gridDim.x) {
             my_ctl[kCtlNext] = 0u;
             my_ctl[kCtlCtasDone] = 0u;
-            if (kFabric && p.world > 1) {
-                // Gather: everything this rank produced is already in rank 0's table; tell rank 0.
-                uint32_t* const arrived = reinterpret_cast<uint32_t*>(p.peer[0] + p.off_ctrl) + kCtlRanksDone;
-                __threadfence_system();
-                atomicAdd_system(arrived, 1u);
-                if (timeline) times[3] = global_ns();
-                if (p.rank == 0) {  // the launch on rank 0 ends only when every rank has delivered
-                    const unsigned long long t0 = global_ns();
-                    while (ld_acquire_sys(arrived) < p.world) {
-                        __nanosleep(128);
-                        if (global_ns() - t0 > p.timeout_ns) {
-                            atomicExch(my_ctl + kCtlError, 2u);
-                            break;
-                        }
-                    }
-                    *arrived = 0u;
-                    if (timeline) times[4] = global_ns();
-                }
-            }
+            my_ctl[kCtlSharedNext] = 0u;
         }
         if (p.timeline) atomicMax(&times[16], global_ns());
     }
 }
 
 // kFabric = false: one GPU owns everything (p.key/p.cnt/p.out/p.ctrl are local).
-// kFabric = true : one of `world` cooperating launches, one per GPU (see sa_cuda_fabric_solve):
-//   rank 0 broadcasts the blob from inside the kernel (NVLS multicast store or per-peer P2P stores,
-//   chunk by chunk, each chunk followed by a release flag), the other ranks start scoring as soon
-//   as the chunks they need have landed; per-sequence keys/counters live on the sequence's home
-//   rank and are updated with system-scope atomics over NVLink; results go straight into rank 0's
-//   table; the last CTA of every rank bumps rank 0's arrival counter and rank 0's last CTA waits
-//   for all of them. No MPI/NCCL call on either path (replaces main.c:149-152,174,195-197).
+// kFabric = true : one of `world` cooperating launches, one per GPU (see sa_cuda_fabric_solve and the
+//   data-movement notes above fabric_prologue); the caller has run fabric_prologue, so s_hdr is valid.
 template <bool kFabric>
-__device__ __forceinline__ void score_body(const KParams& p, const bool prologue_done = false, const bool epilogue_later = false) {
+__device__ __forceinline__ void score_body(const KParams& p, const bool epilogue_later = false) {
     extern __shared__ __align__(16) unsigned char smem[];
     unsigned char* const lut_b = smem;
     unsigned char* const s2 = lut_b + kLutBytes;
@@ -412,30 +441,25 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
     uint32_t* const ctl = reinterpret_cast<uint32_t*>(scan + kWarps);  // [0] item, [1] last flag, [2] first k
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
+    const sa_blob_header* const hdr = kFabric ? &s_hdr : reinterpret_cast<const sa_blob_header*>(p.blob);
     const uint32_t bar = smem_u32(mbar);
     uint32_t parity = 0;
     uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
     unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
-    const bool timeline = p.timeline != 0u && (!kFabric || !prologue_done);
+    const bool timeline = p.timeline != 0u && !kFabric;
     const bool tl_any = p.timeline != 0u;  // slots 11..15: latest CTA to reach each phase of its FIRST item
     if (timeline && tid == 0) atomicMin(&times[0], global_ns());
 
     if (tid == 0) {
         mbar_init(bar, 1);
         mbar_fence_init();
-        if (!prologue_done) s_abort = 0u, s_all_here = 0u;
     }
     __syncthreads();
-
-    if (kFabric && !prologue_done) fabric_prologue(p);
     const bool dead_on_arrival = kFabric && s_abort != 0u;
-    if (timeline && tid == 0) atomicMax(&times[1], global_ns());
 
     // A single-GPU launch gets the header's offsets as kernel parameters (the host has the header):
     // no dependent read of cold global memory before the first item can be fetched.
     const uint32_t off_seqtab = kFabric ? (dead_on_arrival ? 0u : hdr->off_seqtab) : p.h_off_seqtab;
-    const uint32_t off_items = kFabric ? (dead_on_arrival ? 0u : hdr->off_items) : p.h_off_items;
     const uint32_t off_seq1 = kFabric ? (dead_on_arrival ? 0u : hdr->off_seq1) : p.h_off_seq1;
     const uint32_t off_lut = kFabric ? (dead_on_arrival ? 0u : hdr->off_lut) : p.h_off_lut;
     const uint32_t nseq_all = kFabric ? (dead_on_arrival ? 0u : hdr->nseq) : p.h_nseq;
@@ -443,10 +467,14 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
     const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + off_seqtab);
     const sa_tile_item* const fat = reinterpret_cast<const sa_tile_item*>(p.blob + off_fat);
     const unsigned char* const seq1g = p.blob + off_seq1;
-    (void)off_items;
     const uint32_t item_begin = kFabric ? (dead_on_arrival ? 0u : hdr->rank_first_item[p.rank]) : p.item_begin;
     const uint32_t item_end = kFabric ? (dead_on_arrival ? 0u : hdr->rank_first_item[p.rank + 1]) : p.item_end;
     int4* const out = kFabric ? reinterpret_cast<int4*>(p.peer[0] + p.off_out) : p.out;
+    // Ranks other than 0 first stage their share of rank 0's blob: the first n_copy entries of the work
+    // queue are copy items (one chunk each), scoring items follow.
+    PullPlan pp{};
+    if (kFabric && p.rank != 0 && !p.skip_push && !dead_on_arrival) pp = make_pull_plan(*hdr, p.rank);
+    const uint32_t n_copy = pp.total;
 
     // Sequences longer than Seq1 have no candidates: (INT_MIN, 0, 0) as the reference's
     // untouched `max` (cudaFunctions.cu:113,170-172).
@@ -455,15 +483,26 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
             if (seqtab[s].ntiles == 0) out[s] = make_int4(INT_MIN, 0, 0, 0);
     }
 
-    bool first = true;  // CTA-uniform: the first item is blockIdx.x (no queue round trip) and brings the table along
+    // CTA-uniform: the first queue entry is blockIdx.x (no round trip to the queue) — unless copy items exist:
+    // those must only ever be held by CTAs that are running, or a waiting CTA could wait for one that has not started
+    bool fresh = n_copy == 0u;
+    const uint32_t q_base = fresh ? gridDim.x : 0u;
+    bool first = true;  // CTA-uniform: the first scoring item brings the table along
     for (;;) {
         if (tid == 0) {
-            uint32_t it = item_begin + (first ? blockIdx.x : gridDim.x + atomicAdd(&my_ctl[kCtlNext], 1u));
-            if (!kFabric && first && hdr->magic != SA_BLOB_MAGIC) it = 0xFFFFFFFFu;  // never walk memory that is not a packed problem
-            if (kFabric && p.rank != 0 && it < item_end) {  // this sequence's letters may still be in flight
-                const sa_tile_item d = fat[it];
-                const uint32_t bytes = ((uint32_t)d.crow * ((uint32_t)kWarps >> d.wd_log2) + 15u) & ~15u;
-                const bool ok = fabric_bytes_ready(p, hdr, my_ctl, d.off, d.off + bytes);
+            uint32_t it = fresh ? blockIdx.x : q_base + atomicAdd(&my_ctl[kCtlNext], 1u);
+            if (!kFabric && fresh && hdr->magic != SA_BLOB_MAGIC) it = 0xFFFFFFF0u;  // never walk memory that is not a packed problem
+            if (kFabric && it >= n_copy && it - n_copy < item_end - item_begin && p.rank != 0) {
+                // this item's record and letters (and, once per CTA, the shared part) may still be on their way
+                const uint32_t idx = item_begin + (it - n_copy);
+                const uint32_t rec = off_fat + 32u * idx;
+                bool ok = fabric_bytes_ready(p, my_ctl, rec, rec + 32u);
+                if (ok) {
+                    const sa_tile_item d = fat[idx];
+                    const uint32_t bytes = ((uint32_t)d.crow * ((uint32_t)kWarps >> d.wd_log2) + 15u) & ~15u;
+                    ok = fabric_bytes_ready(p, my_ctl, d.off, d.off + bytes);
+                }
+                if (ok && first) ok = fabric_bytes_ready(p, my_ctl, 0u, hdr->off_shared_end);
                 if (!ok) {
                     s_abort = 1u;
                     atomicExch(my_ctl + kCtlError, 1u);
@@ -474,8 +513,18 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
             if (tl_any && first) atomicMax(&times[11], global_ns());
         }
         __syncthreads();  // also: every read of s2/win/csum of the previous item is done
-        const uint32_t item = ctl[0];
-        if (item >= item_end || (kFabric && s_abort != 0u)) break;
+        fresh = false;
+        const uint32_t raw = ctl[0];
+        if (kFabric && s_abort != 0u) break;
+        if (raw < n_copy) {  // copy item: the whole CTA stages one chunk, one thread publishes it
+            const uint32_t chunk = pull_chunk_of(pp, raw);
+            pull_copy(p, *hdr, chunk, tid, kThreads);
+            __syncthreads();
+            if (tid == 0) pull_publish(p, my_ctl, chunk, n_copy);
+            continue;
+        }
+        if (raw - n_copy >= item_end - item_begin) break;
+        const uint32_t item = item_begin + (raw - n_copy);
 
         const sa_tile_item sd = fat[item];  // one self-contained 32-byte record per item
         const uint32_t seq = sd.seq, tile = sd.tile;
@@ -622,11 +671,15 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool prologue
             const int kres = sd.ndiag == 0 ? 0 : first_k_on_diagonal(reinterpret_cast<const int*>(lut_b), s2, seq1g + nwin,
                                                                       sd.len, bestv, scan, csum, &ctl[2]);
             if (tid == 0) {
-                out[seq] = make_int4(bestv, (int)nwin, kres, 0);
                 if (sd.ntiles != 1) {
-                    *keyp = 0ull;  // leave the scratch zeroed for the next launch
+                    *keyp = 0ull;  // leave the scratch zeroed for the next launch ...
                     *cntp = 0u;
+                    // ... and make sure it IS zero before anybody can learn that this solve is over: the row
+                    // below is what lets rank 0's launch end and the next solve's atomics start
+                    if (kFabric) { if (sd.home == p.rank) __threadfence(); else __threadfence_system(); }
                 }
+                if (kFabric) post_result(p, seq, bestv, nwin, (uint32_t)kres);
+                else out[seq] = make_int4(bestv, (int)nwin, kres, 0);
                 if (tl_any && was_first) atomicMax(&times[15], global_ns());
             }
         }
@@ -887,7 +940,7 @@ __device__ __forceinline__ int warp_first_k(const uint32_t* lutlo, const unsigne
 template <bool kFabric>
 __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogue_later = false) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
+    const sa_blob_header* const hdr = kFabric ? &s_hdr : reinterpret_cast<const sa_blob_header*>(p.blob);
     if (!kFabric && hdr->magic != SA_BLOB_MAGIC) return;  // never walk memory that is not a packed problem
     const uint32_t seq1_bytes = (hdr->len1_padded + 15u) & ~15u;
     uint32_t* const lutlo = reinterpret_cast<uint32_t*>(smem);
@@ -899,14 +952,45 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + hdr->off_seqtab);
     const sa_item* const items = reinterpret_cast<const sa_item*>(p.blob + hdr->off_items);
-    const sa_item* const pairs = reinterpret_cast<const sa_item*>(p.blob + hdr->off_pairs);
+    const sa_pair_rec* const pairs = reinterpret_cast<const sa_pair_rec*>(p.blob + hdr->off_pairs);
     const int vmin = hdr->value_min;
+    const int len1 = (int)hdr->len1;
     constexpr uint32_t BIG = kBig;
     const uint32_t bar = smem_u32(mbar);
     uint32_t* const my_ctl = kFabric ? reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) : p.ctrl;
     int4* const out = kFabric ? reinterpret_cast<int4*>(p.peer[0] + p.off_out) : p.out;
     const uint32_t item_begin = kFabric ? hdr->rank_first_item[p.rank] : p.item_begin;
     const uint32_t item_end = kFabric ? hdr->rank_first_item[p.rank + 1] : p.item_end;
+    // Ranks other than 0 stage their share of rank 0's blob first (see fabric_prologue's notes): the
+    // shared part by whole CTAs right here (the CTA-wide start-up below reads it), the rest by single
+    // warps as the first entries of the warp-level work queue.
+    PullPlan pp{};
+    if (kFabric && p.rank != 0 && !p.skip_push) pp = make_pull_plan(*hdr, p.rank);
+    const uint32_t n_copy = pp.total, n_shared = pp.count[0], n_warp_copy = n_copy - n_shared;
+    if (kFabric && n_shared) {
+        __shared__ uint32_t s_chunk;
+        for (;;) {
+            if (tid == 0) s_chunk = atomicAdd(&my_ctl[kCtlSharedNext], 1u);
+            __syncthreads();
+            const uint32_t j = s_chunk;
+            if (j >= n_shared) break;
+            pull_copy(p, *hdr, pp.first[0] + j, tid, kThreads);
+            __syncthreads();
+            if (tid == 0) pull_publish(p, my_ctl, pp.first[0] + j, n_copy);
+        }
+        if (tid == 0) {
+            if (!fabric_bytes_ready(p, my_ctl, 0u, hdr->off_shared_end)) {
+                s_abort = 1u;
+                atomicExch(my_ctl + kCtlError, 1u);
+            }
+            fence_proxy_async();
+        }
+        __syncthreads();
+        if (s_abort != 0u) {
+            if (!epilogue_later) launch_epilogue<kFabric>(p);
+            return;
+        }
+    }
 
     if (p.write_empty) {
         for (uint32_t s = blockIdx.x * kThreads + tid; s < hdr->nseq; s += gridDim.x * kThreads)
@@ -934,10 +1018,19 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
     uint32_t* const pw = prof + warp * (SA_STREAM_ROW_BLOCK * SA_ALPHABET);
     const uint32_t d0 = lane * kR;
     for (;;) {
-        uint32_t item = 0;
-        if (lane == 0) item = item_begin + atomicAdd(&my_ctl[kCtlNext], 1u);
-        item = __shfl_sync(0xFFFFFFFFu, item, 0);
-        if (item >= item_end || (kFabric && *reinterpret_cast<volatile uint32_t*>(&s_abort) != 0u)) break;
+        uint32_t raw = 0;
+        if (lane == 0) raw = atomicAdd(&my_ctl[kCtlNext], 1u);
+        raw = __shfl_sync(0xFFFFFFFFu, raw, 0);
+        if (kFabric && *reinterpret_cast<volatile uint32_t*>(&s_abort) != 0u) break;
+        if (raw < n_warp_copy) {  // copy item: this warp stages one chunk of its rank's share
+            const uint32_t chunk = pull_chunk_of(pp, n_shared + raw);
+            pull_copy(p, *hdr, chunk, lane, 32u);
+            __syncwarp();
+            if (lane == 0) pull_publish(p, my_ctl, chunk, n_copy);
+            continue;
+        }
+        if (raw - n_warp_copy >= item_end - item_begin) break;
+        const uint32_t item = item_begin + (raw - n_warp_copy);
         if (kFabric && p.timeline && lane == 0) {  // when were 25 / 50 / 75 % of this rank's items handed out?
             const uint32_t n_it = item_end - item_begin, k = item - item_begin;
             unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
@@ -945,23 +1038,38 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
             if (k == n_it / 2) times[9] = global_ns();
             if (k == (n_it / 4) * 3) times[10] = global_ns();
         }
-        const uint32_t pid = items[item].seq, tile = items[item].tile;
-        const uint32_t ia = pairs[pid].seq, ib = pairs[pid].tile;
-        const bool has_b = ib != SA_NO_SEQ;
-        const sa_seq_desc da = seqtab[ia];
-        sa_seq_desc db = da;
-        if (has_b) db = seqtab[ib];
-        const uint32_t rows = da.crow, n0 = tile * SA_DIAG_PER_WARP;
-        const unsigned char* const gA = p.blob + da.off;
-        const unsigned char* const gB = p.blob + db.off;
-        unsigned long long* const keyA_p = (kFabric ? reinterpret_cast<unsigned long long*>(p.peer[da.home] + p.off_key) : p.key) + ia;
-        unsigned long long* const keyB_p = (kFabric ? reinterpret_cast<unsigned long long*>(p.peer[da.home] + p.off_key) : p.key) + (has_b ? ib : ia);
-        unsigned int* const cnt_p = (kFabric ? reinterpret_cast<unsigned int*>(p.peer[da.home] + p.off_cnt) : p.cnt) + pid;
-        if (kFabric && p.rank != 0) {  // the two sequences' letters may still be in flight from rank 0
+        if (kFabric && p.rank != 0) {  // the item and its pair record may still be on their way
             uint32_t ok = 1u;
             if (lane == 0) {
-                ok = fabric_bytes_ready(p, hdr, my_ctl, da.off, da.off + rows) ? 1u : 0u;
-                if (ok && has_b) ok = fabric_bytes_ready(p, hdr, my_ctl, db.off, db.off + rows) ? 1u : 0u;
+                const uint32_t io = hdr->off_items + 8u * item;
+                ok = fabric_bytes_ready(p, my_ctl, io, io + 8u) ? 1u : 0u;
+                if (ok) {
+                    const uint32_t po = hdr->off_pairs + 32u * items[item].seq;
+                    ok = fabric_bytes_ready(p, my_ctl, po, po + 32u) ? 1u : 0u;
+                }
+                if (!ok) {
+                    *reinterpret_cast<volatile uint32_t*>(&s_abort) = 1u;
+                    atomicExch(my_ctl + kCtlError, 1u);
+                }
+            }
+            if (!__shfl_sync(0xFFFFFFFFu, ok, 0)) break;
+        }
+        const uint32_t pid = items[item].seq, tile = items[item].tile;
+        const sa_pair_rec pr = pairs[pid];
+        const uint32_t ia = pr.a, ib = pr.b;
+        const bool has_b = ib != SA_NO_SEQ;
+        const int ndiag_a = len1 - (int)pr.len_a, ndiag_b = len1 - (int)pr.len_b;
+        const uint32_t rows = pr.crow, n0 = tile * SA_DIAG_PER_WARP;
+        const unsigned char* const gA = p.blob + pr.off_a;
+        const unsigned char* const gB = p.blob + pr.off_b;
+        unsigned long long* const keyA_p = (kFabric ? reinterpret_cast<unsigned long long*>(p.peer[pr.home] + p.off_key) : p.key) + ia;
+        unsigned long long* const keyB_p = (kFabric ? reinterpret_cast<unsigned long long*>(p.peer[pr.home] + p.off_key) : p.key) + (has_b ? ib : ia);
+        unsigned int* const cnt_p = (kFabric ? reinterpret_cast<unsigned int*>(p.peer[pr.home] + p.off_cnt) : p.cnt) + ia;
+        if (kFabric && p.rank != 0) {  // the two sequences' letters may still be on their way
+            uint32_t ok = 1u;
+            if (lane == 0) {
+                ok = fabric_bytes_ready(p, my_ctl, pr.off_a, pr.off_a + rows) ? 1u : 0u;
+                if (ok && has_b) ok = fabric_bytes_ready(p, my_ctl, pr.off_b, pr.off_b + rows) ? 1u : 0u;
                 if (!ok) {
                     *reinterpret_cast<volatile uint32_t*>(&s_abort) = 1u;
                     atomicExch(my_ctl + kCtlError, 1u);
@@ -1026,15 +1134,15 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
             const int t0a = (int)(P[r] & 0xFFFFu) + vb, t1a = (int)(P[r + 1] & 0xFFFFu) + vb;
             const int t0b = (int)(P[r] >> 16) + vb, t1b = (int)(P[r + 1] >> 16) + vb;
             const int ma = (int)(best[r] & 0xFFFFu) - (int)BIG, mb = (int)(best[r] >> 16) - (int)BIG;
-            if (da.ndiag == 0) {
+            if (ndiag_a == 0) {
                 if (n == 0) keyA = pack_key(t0a, 0u);
-            } else if (n < (uint32_t)da.ndiag) {
+            } else if (n < (uint32_t)ndiag_a) {
                 keyA = umax64(keyA, pack_key(t1a + ma, n));
             }
             if (has_b) {
-                if (db.ndiag == 0) {
+                if (ndiag_b == 0) {
                     if (n == 0) keyB = pack_key(t0b, 0u);
-                } else if (n < (uint32_t)db.ndiag) {
+                } else if (n < (uint32_t)ndiag_b) {
                     keyB = umax64(keyB, pack_key(t1b + mb, n));
                 }
             }
@@ -1045,45 +1153,58 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
             keyB = umax64(keyB, __shfl_xor_sync(0xFFFFFFFFu, keyB, o));
         }
         uint32_t last = 0;
+        const bool home_is_me = !kFabric || pr.home == p.rank;
         if (lane == 0) {
-            if (kFabric) {
+            if (pr.ntiles == 1) {  // the pair's only tile: nothing to combine, no atomics
+                last = 1u;
+            } else if (kFabric) {
                 atomicMax_system(keyA_p, keyA);
                 if (has_b) atomicMax_system(keyB_p, keyB);
-                if (da.home == p.rank) __threadfence(); else __threadfence_system();
-                last = (atomicAdd_system(cnt_p, 1u) + 1u == da.ntiles) ? 1u : 0u;
+                if (home_is_me) __threadfence(); else __threadfence_system();
+                last = (atomicAdd_system(cnt_p, 1u) + 1u == pr.ntiles) ? 1u : 0u;
             } else {
                 atomicMax(keyA_p, keyA);
                 if (has_b) atomicMax(keyB_p, keyB);
                 __threadfence();
-                last = (atomicAdd(cnt_p, 1u) + 1u == da.ntiles) ? 1u : 0u;
+                last = (atomicAdd(cnt_p, 1u) + 1u == pr.ntiles) ? 1u : 0u;
             }
         }
         last = __shfl_sync(0xFFFFFFFFu, last, 0);
         if (last) {  // this warp delivered the pair's last tile: finish both sequences
-            for (int half = 0; half < (has_b ? 2 : 1); ++half) {
-                const sa_seq_desc& sd = half == 0 ? da : db;
-                const uint32_t sidx = half == 0 ? ia : ib;
-                unsigned long long* const kp = half == 0 ? keyA_p : keyB_p;
-                unsigned long long fk = 0ull;
+            unsigned long long fka = keyA, fkb = keyB;
+            if (pr.ntiles != 1) {
                 if (lane == 0) {
                     if (kFabric) {
-                        if (da.home == p.rank) __threadfence(); else __threadfence_system();
-                        fk = atomicMax_system(kp, 0ull);
+                        if (home_is_me) __threadfence(); else __threadfence_system();
+                        fka = atomicMax_system(keyA_p, 0ull);
+                        if (has_b) fkb = atomicMax_system(keyB_p, 0ull);
                     } else {
                         __threadfence();
-                        fk = atomicMax(kp, 0ull);
+                        fka = atomicMax(keyA_p, 0ull);
+                        if (has_b) fkb = atomicMax(keyB_p, 0ull);
                     }
+                    // leave the scratch zeroed for the next launch, and make sure it IS zero before the rows
+                    // below can tell anybody that this solve is over
+                    *keyA_p = 0ull;
+                    if (has_b) *keyB_p = 0ull;
+                    *cnt_p = 0u;
+                    if (kFabric) { if (home_is_me) __threadfence(); else __threadfence_system(); }
                 }
-                fk = __shfl_sync(0xFFFFFFFFu, fk, 0);
+                fka = __shfl_sync(0xFFFFFFFFu, fka, 0);
+                fkb = __shfl_sync(0xFFFFFFFFu, fkb, 0);
+            }
+            for (int half = 0; half < (has_b ? 2 : 1); ++half) {
+                const uint32_t sidx = half == 0 ? ia : ib;
+                const unsigned long long fk = half == 0 ? fka : fkb;
+                const int nd = half == 0 ? ndiag_a : ndiag_b;
                 const int bestv = (int)((uint32_t)(fk >> 32) ^ 0x80000000u);
                 const uint32_t nwin = 0xFFFFFFFFu - (uint32_t)(fk & 0xFFFFFFFFull);
-                const int kres = sd.ndiag == 0 ? 0 : warp_first_k(lutlo, half == 0 ? gA : gB, seq1s + nwin, sd.len, bestv, vmin, lane);
+                const int kres = nd == 0 ? 0 : warp_first_k(lutlo, half == 0 ? gA : gB, seq1s + nwin, half == 0 ? pr.len_a : pr.len_b, bestv, vmin, lane);
                 if (lane == 0) {
-                    out[sidx] = make_int4(bestv, (int)nwin, kres, 0);
-                    *kp = 0ull;
+                    if (kFabric) post_result(p, sidx, bestv, nwin, (uint32_t)kres);
+                    else out[sidx] = make_int4(bestv, (int)nwin, kres, 0);
                 }
             }
-            if (lane == 0) *cnt_p = 0u;
         }
     }
     __syncthreads();
@@ -1093,8 +1214,8 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
 __global__ void __launch_bounds__(kThreads, 2) sa_score_stream_kernel(const KParams p) { stream_body<false>(p); }
 
 // One fabric kernel for both modes: ranks other than 0 launch before they know anything about
-// the problem, so the mode is read from the blob header once the broadcast prefix has landed.
-__global__ void __launch_bounds__(kThreads, 2) sa_score_fabric_kernel(const KParams p) {
+// the problem, so the mode is read from the header packet. hdr0: rank 0's host copy of the header.
+__global__ void __launch_bounds__(kThreads, 2) sa_score_fabric_kernel(const __grid_constant__ KParams p, const __grid_constant__ sa_blob_header hdr0) {
     unsigned long long* const times = reinterpret_cast<unsigned long long*>(reinterpret_cast<uint32_t*>(p.peer[p.rank] + p.off_ctrl) + kCtlTimes);
     if (threadIdx.x == 0) {
         s_abort = 0u;
@@ -1102,14 +1223,12 @@ __global__ void __launch_bounds__(kThreads, 2) sa_score_fabric_kernel(const KPar
         if (p.timeline) atomicMin(&times[0], global_ns());
     }
     __syncthreads();
-    fabric_prologue(p);
-    __syncthreads();
+    fabric_prologue(p, hdr0);
     if (p.timeline && threadIdx.x == 0) atomicMax(&times[1], global_ns());
-    const sa_blob_header* const hdr = reinterpret_cast<const sa_blob_header*>(p.blob);
-    if (s_abort == 0u && (hdr->flags & SA_FLAG_STREAM_MODE))
+    if (s_abort == 0u && (s_hdr.flags & SA_FLAG_STREAM_MODE))
         stream_body<true>(p, true);
     else
-        score_body<true>(p, true, true);
+        score_body<true>(p, true);
     launch_epilogue<true>(p);
 }
 
@@ -1513,11 +1632,15 @@ int sa_fabric_layout(uint32_t max_seq, size_t max_blob_bytes, sa_fabric_layout_t
     size_t off = 0;
     out->off_ctrl = (uint32_t)off;
     off += round_up_sz((kCtlFlags + kMaxChunks) * 4, 256);
+    out->off_hdr_ll = (uint32_t)off;  // header packet: one (epoch | word) pair per header word
+    off += round_up_sz(kHdrWords * 8, 256);
     out->off_key = (uint32_t)off;
     off += key_bytes(max_seq);
     out->off_cnt = (uint32_t)off;
     off += cnt_bytes(max_seq);
     out->off_out = (uint32_t)off;
+    off += round_up_sz((size_t)max_seq * 16, 256);
+    out->off_out_ll = (uint32_t)off;  // result rows as they arrive: two self-validating words each
     off += round_up_sz((size_t)max_seq * 16, 256);
     out->off_blob = (uint32_t)off;
     off += round_up_sz(max_blob_bytes, 256);
@@ -1576,6 +1699,8 @@ int sa_cuda_fabric_solve(const sa_fabric_desc* f, const sa_blob_header* header, 
     p.world = f->world;
     p.epoch = f->epoch;
     p.off_ctrl = f->layout.off_ctrl;
+    p.off_hdr_ll = f->layout.off_hdr_ll;
+    p.off_out_ll = f->layout.off_out_ll;
     p.off_key = f->layout.off_key;
     p.off_cnt = f->layout.off_cnt;
     p.off_out = f->layout.off_out;
@@ -1599,7 +1724,8 @@ int sa_cuda_fabric_solve(const sa_fabric_desc* f, const sa_blob_header* header, 
         }
     }
     const uint32_t grid = (uint32_t)di->sm_count * 2u;
-    sa_score_fabric_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+    static const sa_blob_header no_header{};  // ranks other than 0 receive the header through the fabric
+    sa_score_fabric_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p, f->rank == 0 ? *header : no_header);
     SA_CUDA_TRY(cudaGetLastError());
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return SA_OK;

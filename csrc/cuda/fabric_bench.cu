@@ -12,6 +12,7 @@
 #include <cstdint>
 #include <string>
 
+#include "ptx_helpers.cuh"
 #include "seqalign.h"
 
 namespace {
@@ -31,24 +32,7 @@ struct BParams {
     unsigned long long nkeys;
 };
 
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
-    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ void multimem_st_v4(void* a, int4 v) {
-    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a), "r"(v.x), "r"(v.y), "r"(v.z),
-                 "r"(v.w)
-                 : "memory");
-}
-__device__ __forceinline__ unsigned long long global_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
+using namespace sa_ptx;  // csrc/cuda/ptx_helpers.cuh
 
 __global__ void __launch_bounds__(kThreads) bcast_kernel(const BParams p) {
     const uint32_t tid = threadIdx.x;

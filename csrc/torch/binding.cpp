@@ -12,7 +12,7 @@ namespace {
 const sa_blob_header* header_of(const at::Tensor& header_cpu) {
     TORCH_CHECK(header_cpu.device().is_cpu() && header_cpu.scalar_type() == at::kByte && header_cpu.is_contiguous() &&
                     header_cpu.numel() >= (int64_t)sizeof(sa_blob_header),
-                "header must be a contiguous CPU uint8 tensor holding the blob's first 256 bytes");
+                "header must be a contiguous CPU uint8 tensor holding the blob's first sizeof(sa_blob_header) = 1024 bytes");
     const auto* h = reinterpret_cast<const sa_blob_header*>(header_cpu.data_ptr());
     TORCH_CHECK(h->magic == SA_BLOB_MAGIC && h->version == SA_BLOB_VERSION, "not a packed problem of this version");
     return h;

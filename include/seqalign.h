@@ -139,6 +139,9 @@ size_t sa_format(const int32_t* results, int32_t nseq, char* buf, size_t cap);
 #define SA_MODE_TILE 1
 #define SA_MODE_PAIR 2
 #define SA_MODE_STREAM 3
+/* OR into the mode: deal TILE items to the GPUs tile by tile even when sequences are plentiful, so that
+ * one sequence's offset range is split over GPUs and reduced with the cross-GPU argmax (also SA_SPLIT_TILES=1). */
+#define SA_MODE_SPLIT_TILES 0x100
 #define SA_FLAG_PAIR_MODE 1u
 #define SA_FLAG_STREAM_MODE 2u
 #define SA_STREAM_MIN_ITEMS_PER_GPU 16384u /* AUTO uses STREAM only with several items per resident warp */
@@ -245,6 +248,11 @@ int sa_blob_execute_cpu(const void* blob, size_t blob_bytes, int32_t* out4);
 int sa_blob_score_items_cpu(const void* blob, size_t blob_bytes, uint32_t first_item,
                             uint32_t last_item, uint64_t* keys);
 int sa_blob_finalize_cpu(const void* blob, size_t blob_bytes, const uint64_t* keys, int32_t* out4);
+/* The byte ranges of a blob that rank `rank` of a multi-GPU solve reads: [0] the shared part
+ * (header + table + Seq1: the MPI_Bcast of main.c:149-152), [1] its slice of the item list, [2] of the
+ * tile-item / pair records, [3] the letters of the sequences it scores (the MPI_Scatter of main.c:174).
+ * The fabric kernel pulls exactly these (rounded out to chunks); the CPU world scatters exactly these. */
+int sa_blob_rank_ranges(const sa_blob_header* h, uint32_t rank, uint32_t lo[4], uint32_t hi[4]);
 
 /* The work partition over `world` GPUs (new-build analogue of main.c:110-121) is part
  * of the plan: whole sequences are dealt to the least-loaded rank, costliest first;
@@ -262,7 +270,7 @@ int sa_cuda_scratch_init(void* d_scratch, size_t bytes, void* stream);
 
 /* Solve a packed blob that already sits in device memory.
  *   d_blob     device pointer to the blob (16-byte aligned)
- *   header     HOST copy of the blob's first 256 bytes (sizes the launch; no D2H needed)
+ *   header     HOST copy of the blob's header (sizeof(sa_blob_header) bytes) (sizes the launch; no D2H needed)
  *   d_out      device int32[4*nseq]: score, n, k, 0 per sequence
  *   d_scratch  device scratch of sa_cuda_scratch_bytes(nseq), zeroed once with
  *              sa_cuda_scratch_init (the kernel leaves it zeroed again)
@@ -329,10 +337,10 @@ void sa_session_last_bytes(const sa_session* s, uint64_t* h2d, uint64_t* d2h);
  * atomics in the home rank's memory; results are written straight into rank 0's table and the
  * last CTA of each rank signals rank 0. The host only exchanges buffer mappings once
  * (bootstrap) — no MPI/NCCL call on the data path. */
-#define SA_FABRIC_MAX_CHUNKS 1024u
+#define SA_FABRIC_MAX_CHUNKS 16384u
 
 typedef struct sa_fabric_layout_t {
-    uint32_t off_ctrl, off_key, off_cnt, off_out, off_blob;
+    uint32_t off_ctrl, off_hdr_ll, off_key, off_cnt, off_out, off_out_ll, off_blob;
     uint32_t max_seq;
     uint64_t max_blob_bytes;
     uint64_t total_bytes; /* size of the symmetric buffer every rank must allocate */

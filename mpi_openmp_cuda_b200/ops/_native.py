@@ -33,11 +33,14 @@ class BlobHeader(C.Structure):
         ("max_rows_padded", C.c_uint32), ("max_window_bytes", C.c_uint32), ("chunk_bytes", C.c_uint32), ("nchunks", C.c_uint32), ("pad0", C.c_uint32),
         ("total_cells", C.c_uint64), ("padded_cells", C.c_uint64),
         ("world", C.c_uint32), ("rank_first_item", C.c_uint32 * (SA_MAX_WORLD + 1)),
-        ("value_min", C.c_int32), ("value_range", C.c_uint32), ("off_pairs", C.c_uint32), ("npairs", C.c_uint32), ("off_tile_items", C.c_uint32), ("reserved", C.c_uint32 * 15),
+        ("value_min", C.c_int32), ("value_range", C.c_uint32), ("off_pairs", C.c_uint32), ("npairs", C.c_uint32), ("off_tile_items", C.c_uint32),
+        ("off_shared_end", C.c_uint32), ("rank_first_pair", C.c_uint32 * (SA_MAX_WORLD + 1)),
+        ("rank_seq2_lo", C.c_uint32 * SA_MAX_WORLD), ("rank_seq2_hi", C.c_uint32 * SA_MAX_WORLD),
+        ("reserved", C.c_uint32 * 157),
     ]
 
 
-assert C.sizeof(BlobHeader) == 256
+assert C.sizeof(BlobHeader) == 1024
 
 
 class SeqDesc(C.Structure):
@@ -93,6 +96,7 @@ def core() -> C.CDLL:
     lib.sa_blob_execute_cpu.argtypes = [C.c_void_p, sz, i32p]
     lib.sa_blob_score_items_cpu.argtypes = [C.c_void_p, sz, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
     lib.sa_blob_finalize_cpu.argtypes = [C.c_void_p, sz, C.POINTER(C.c_uint64), i32p]
+    lib.sa_blob_rank_ranges.argtypes = [C.POINTER(BlobHeader), C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     return lib
 
 

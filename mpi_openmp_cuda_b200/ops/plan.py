@@ -49,6 +49,13 @@ class PackedBlob:
                        ("ntiles", "<u2"), ("wd_log2", "u1"), ("home", "u1")])
         return raw.view(dt)
 
+    def pair_records(self) -> np.ndarray:
+        """STREAM mode: the self-contained 32-byte record per pair (sa_pair_rec)."""
+        raw = self.numpy()[self.header.off_pairs : self.header.off_pairs + 32 * int(self.header.npairs)]
+        dt = np.dtype([("a", "<u4"), ("b", "<u4"), ("off_a", "<u4"), ("off_b", "<u4"), ("len_a", "<u2"), ("len_b", "<u2"),
+                       ("crow", "<u2"), ("ntiles", "<u2"), ("home", "u1"), ("pad8", "u1", 3), ("pad", "<u4")])
+        return raw.view(dt)
+
     def items(self) -> np.ndarray:
         raw = self.numpy()[self.header.off_items : self.header.off_items + 8 * self.nitems]
         return raw.view(np.dtype([("seq", "<u4"), ("tile", "<u4")]))
@@ -57,17 +64,25 @@ class PackedBlob:
 MODES = {"auto": N.SA_MODE_AUTO, "tile": N.SA_MODE_TILE, "pair": N.SA_MODE_PAIR, "stream": N.SA_MODE_STREAM}
 
 
-def blob_size(problem, world: int = 1, mode: str = "auto") -> int:
+SPLIT_TILES = 0x100  # SA_MODE_SPLIT_TILES
+
+
+def _mode(mode: str, split_tiles: bool) -> int:
+    return MODES[mode] | (SPLIT_TILES if split_tiles else 0)
+
+
+def blob_size(problem, world: int = 1, mode: str = "auto", split_tiles: bool = False) -> int:
     need = C.c_size_t()
-    N.check(N.core().sa_plan_pack_mode(problem.handle, world, MODES[mode], None, 0, C.byref(need)))
+    N.check(N.core().sa_plan_pack_mode(problem.handle, world, _mode(mode, split_tiles), None, 0, C.byref(need)))
     return int(need.value)
 
 
-def plan_pack(problem, world: int = 1, pinned: bool = False, out=None, mode: str = "auto") -> PackedBlob:
+def plan_pack(problem, world: int = 1, pinned: bool = False, out=None, mode: str = "auto", split_tiles: bool = False) -> PackedBlob:
     """Plan the tiling, partition over `world` GPUs and pack. Raises NativeError with
     code SA_ERR_UNSUPPORTED when the input is outside the GPU executor's limits.
-    mode: 'auto' | 'tile' (any input) | 'pair' (u16x2 throughput mode, single GPU)."""
-    need = blob_size(problem, world, mode)
+    mode: 'auto' | 'tile' (any input) | 'pair' (u16x2 throughput mode, single GPU) | 'stream';
+    split_tiles: deal TILE items tile by tile so that single sequences are split over GPUs."""
+    need = blob_size(problem, world, mode, split_tiles)
     if out is not None:
         buf = out
         if buf.numel() < need:
@@ -82,7 +97,7 @@ def plan_pack(problem, world: int = 1, pinned: bool = False, out=None, mode: str
         buf = np.empty(need, dtype=np.uint8)
         ptr = buf.ctypes.data
     got = C.c_size_t()
-    N.check(N.core().sa_plan_pack_mode(problem.handle, world, MODES[mode], C.c_void_p(ptr), need, C.byref(got)))
+    N.check(N.core().sa_plan_pack_mode(problem.handle, world, _mode(mode, split_tiles), C.c_void_p(ptr), need, C.byref(got)))
     hdr = N.BlobHeader.from_buffer_copy(C.string_at(ptr, C.sizeof(N.BlobHeader)))
     return PackedBlob(buf, int(got.value), hdr)
 

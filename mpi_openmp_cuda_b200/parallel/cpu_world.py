@@ -1,9 +1,13 @@
 """CPU-only multi-process configuration (BASELINE.json configs[0]: "2 ranks on CPU, scoring kernel
 swapped for its CPU reference; plumbing and output-diff check, no GPU").
 
-Same roles as the GPU fabric, with gloo collectives standing in for the in-kernel ones: rank 0
-plans + packs, the blob is broadcast, every rank scores its own item range into packed keys
-with the CPU walk of the kernel's tile logic, keys are max-reduced, rank 0 finalises."""
+Same roles and the same data movement as the GPU fabric, with gloo collectives standing in for the
+in-kernel ones: rank 0 plans + packs; the 1 KB header is broadcast; every rank then receives ONLY
+the byte ranges the header assigns to it (`sa_blob_rank_ranges`: the shared table/Seq1 plus its own
+slices of the item list, the records and the Seq2 letters — the reference's MPI_Bcast + MPI_Scatter,
+main.c:149-152,174) into an otherwise zero-filled blob; it scores its own item range into packed
+keys with the CPU walk of the kernel's tile logic; keys are max-reduced; rank 0 finalises. Scoring
+from the sparse blob is the proof that a rank's ranges cover everything its kernel reads."""
 from __future__ import annotations
 
 import ctypes as C
@@ -15,20 +19,40 @@ import torch.distributed as dist
 from ..ops import _native as N
 from ..ops import plan
 
+_HDR = C.sizeof(N.BlobHeader)
+
+
+def rank_ranges(hdr: N.BlobHeader, rank: int) -> list[tuple[int, int]]:
+    lo, hi = (C.c_uint32 * 4)(), (C.c_uint32 * 4)()
+    N.check(N.core().sa_blob_rank_ranges(C.byref(hdr), rank, lo, hi))
+    return [(int(a), int(b)) for a, b in zip(lo, hi) if b > a]
+
 
 def solve_cpu_world(problem=None) -> np.ndarray | None:
     rank, world = dist.get_rank(), dist.get_world_size()
+    head = torch.zeros(_HDR, dtype=torch.uint8)
     if rank == 0:
         blob = plan.plan_pack(problem, world)
-        size = torch.tensor([blob.nbytes], dtype=torch.int64)
+        full = blob.numpy()[: blob.nbytes]
+        head.copy_(torch.from_numpy(full[:_HDR].copy()))
+    dist.broadcast(head, 0)  # the header packet
+    hdr = N.BlobHeader.from_buffer_copy(head.numpy().tobytes())
+    nbytes = int(hdr.total_bytes)
+    mine = rank_ranges(hdr, rank)
+    if rank == 0:
+        arr = full
+        for r in range(1, world):  # the scatter: rank r gets its ranges, back to back, and nothing else
+            parts = [torch.from_numpy(full[a:b].copy()) for a, b in rank_ranges(hdr, r)]
+            dist.send(torch.cat(parts) if parts else torch.zeros(1, dtype=torch.uint8), r)
     else:
-        size = torch.zeros(1, dtype=torch.int64)
-    dist.broadcast(size, 0)
-    nbytes = int(size.item())
-    data = torch.from_numpy(blob.numpy()[:nbytes]) if rank == 0 else torch.empty(nbytes, dtype=torch.uint8)
-    dist.broadcast(data, 0)  # MPI_Bcast + MPI_Scatter of the reference in one message
-    arr = data.numpy()
-    hdr = N.BlobHeader.from_buffer_copy(arr[:256].tobytes())
+        got = torch.zeros(max(1, sum(b - a for a, b in mine)), dtype=torch.uint8)
+        dist.recv(got, 0)
+        arr = np.zeros(nbytes, dtype=np.uint8)  # everything this rank was NOT sent stays zero
+        arr[:_HDR] = head.numpy()
+        at = 0
+        for a, b in mine:
+            arr[a:b] = got.numpy()[at : at + (b - a)]
+            at += b - a
     first, last = int(hdr.rank_first_item[rank]), int(hdr.rank_first_item[rank + 1])
     keys = np.zeros(max(int(hdr.nseq), 1), dtype=np.uint64)
     N.check(N.core().sa_blob_score_items_cpu(C.c_void_p(arr.ctypes.data), nbytes, first, last,

@@ -67,13 +67,31 @@ class DistributedSolver:
             raise RuntimeError(f"fabric wait timed out on rank {self.rank} (code {err}): a peer GPU did not deliver")
 
     def solve(self, problem=None) -> np.ndarray | None:
-        """Collective: every rank calls solve(); rank 0 passes the problem and gets int32[nseq,3]."""
+        """Collective: every rank calls solve(); rank 0 passes the problem and gets int32[nseq,3].
+        An input outside the GPU executor's limits (Seq2 > 8192 letters, more than five distinct non-letter
+        bytes, very large weights) is solved by the CPU oracle on rank 0 — as `final --gpus 1` does — while
+        the fabric runs an empty problem, so that the other ranks' kernels return at once instead of
+        waiting for a header that would never come."""
         if self.rank == 0:
-            blob = self.pack(problem)
+            from ..ops import _native as N
+            from ..ops import oracle
+
+            fallback = None
+            try:
+                blob = self.pack(problem)
+                if blob.nbytes > self.fabric.layout.max_blob_bytes or blob.nseq > self.fabric.layout.max_seq:
+                    raise N.NativeError(N.SA_ERR_UNSUPPORTED, "problem exceeds the fabric's capacity")
+            except N.NativeError as e:
+                if e.code != N.SA_ERR_UNSUPPORTED:
+                    raise
+                fallback = oracle.solve_cpu(problem, "fast")
+                from ..utils.parser import Problem
+
+                blob = self.pack(Problem.from_parts((1, 1, 1, 1), b"A", []))
             self.launch_packed(blob)
             res = self.fetch(blob.nseq)
             self.check()
-            return res.copy()
+            return fallback if fallback is not None else res.copy()
         self.launch_packed(None)
         self.fetch(0)
         self.check()

@@ -2,9 +2,11 @@
 every peer (NVLink 5 / NVSwitch), plus the NVLS multicast alias when the platform has one.
 
 torch.distributed (+ torch symmetric memory) is used ONLY here, to exchange the mappings once.
-The data path — broadcast of the input, argmax reduce, gather of results — runs inside
-`sa_score_fabric_kernel` (csrc/cuda/align_kernel.cu) and replaces the reference's
-MPI_Bcast/Scatter/Gather (main.c:149-152,174,195-197).
+The data path runs inside `sa_score_fabric_kernel` (csrc/cuda/align_kernel.cu) and replaces the
+reference's MPI_Bcast/Scatter/Gather (main.c:149-152,174,195-197): rank 0 multicasts the 1 KB
+header as a flag-in-data packet, every other rank pulls the shared table/Seq1 and its OWN rows
+from rank 0's buffer (a scatter: nothing is sent that is not consumed), finished rows are stored
+straight into rank 0's table as self-validating words, split sequences reduce with atomicMax.sys.
 """
 from __future__ import annotations
 
@@ -18,8 +20,8 @@ from ..ops import _native as N
 
 
 class FabricLayout(C.Structure):
-    _fields_ = [("off_ctrl", C.c_uint32), ("off_key", C.c_uint32), ("off_cnt", C.c_uint32),
-                ("off_out", C.c_uint32), ("off_blob", C.c_uint32), ("max_seq", C.c_uint32),
+    _fields_ = [("off_ctrl", C.c_uint32), ("off_hdr_ll", C.c_uint32), ("off_key", C.c_uint32), ("off_cnt", C.c_uint32),
+                ("off_out", C.c_uint32), ("off_out_ll", C.c_uint32), ("off_blob", C.c_uint32), ("max_seq", C.c_uint32),
                 ("max_blob_bytes", C.c_uint64), ("total_bytes", C.c_uint64)]
 
 
@@ -107,10 +109,13 @@ class Fabric:
 
     def read_timeline(self) -> dict:
         """After a synchronised launch with SA_FABRIC_TIMELINE=1: microseconds since this rank's first CTA started."""
-        t = self.buf[self.layout.off_ctrl + 64 : self.layout.off_ctrl + 64 + 88].view(torch.int64).cpu().tolist()
-        names = ["start", "prefix_ready", "items_done", "arrival_sent", "all_arrived", "all_here_seen"]
+        t = self.buf[self.layout.off_ctrl + 64 : self.layout.off_ctrl + 64 + 8 * 18].view(torch.int64).cpu().tolist()
+        names = {1: "header_known", 17: "first_chunk_staged", 5: "all_chunks_staged", 11: "first_item_known",
+                 12: "first_tma_landed", 13: "first_scan_done", 15: "first_result_posted", 2: "items_done",
+                 4: "all_results_validated", 16: "last_cta_exit"}
         big = torch.iinfo(torch.int64).max
-        out = {n: (None if v in (0, big) else round((v - t[0]) / 1e3, 2)) for n, v in zip(names, t)}
+        out = {"start": 0.0}
+        out.update({n: (None if t[i] in (0, big) else round((t[i] - t[0]) / 1e3, 2)) for i, n in names.items()})
         out["items_that_waited"] = t[6]
         out["wait_us_total"] = round(t[7] / 1e3, 1)
         out["quartiles_handed_out"] = [None if v == 0 else round((v - t[0]) / 1e3, 1) for v in t[8:11]]
@@ -144,10 +149,10 @@ class Fabric:
         d.epoch = self.epoch
         d.pad0 = (1 if self.timeline else 0) | (2 if resident else 0)
         if self.timeline:  # slot 0 is a running minimum: re-arm it (and the maxima) before every launch
-            t = self.buf[self.layout.off_ctrl + 64 : self.layout.off_ctrl + 64 + 88].view(torch.int64)
+            t = self.buf[self.layout.off_ctrl + 64 : self.layout.off_ctrl + 64 + 8 * 18].view(torch.int64)
             t.zero_()
             t[0] = torch.iinfo(torch.int64).max
-            t[5] = torch.iinfo(torch.int64).max
+            t[17] = torch.iinfo(torch.int64).max
         stream = torch.cuda.current_stream(self.device).cuda_stream
         hdr = C.byref(header) if header is not None else None
         with torch.cuda.device(self.device):

@@ -18,11 +18,11 @@ def test_reference_partition_matches_main_c():
 def test_descriptor_struct_sizes_match_the_header():
     from mpi_openmp_cuda_b200.ops import _native as N
 
-    assert C.sizeof(N.BlobHeader) == 256 and C.sizeof(N.SeqDesc) == 16
+    assert C.sizeof(N.BlobHeader) == 1024 and C.sizeof(N.SeqDesc) == 16
     try:
         from mpi_openmp_cuda_b200.parallel.fabric import FabricDesc, FabricLayout
     except Exception as e:  # torch.distributed missing would be an environment problem, not ours
         pytest.skip(str(e))
-    assert C.sizeof(FabricLayout) == 40
-    assert C.sizeof(FabricDesc) == 24 + 8 * N.SA_MAX_WORLD + 8 + 40
+    assert C.sizeof(FabricLayout) == 48
+    assert C.sizeof(FabricDesc) == 24 + 8 * N.SA_MAX_WORLD + 8 + 48
     assert FabricDesc.peer_base.offset == 24 and FabricDesc.layout.offset == 24 + 8 * N.SA_MAX_WORLD + 8

@@ -107,5 +107,41 @@ def test_dead_peer_times_out_instead_of_hanging():
     err = int(bufs[1][lay.off_ctrl + 12 : lay.off_ctrl + 16].view(torch.int32).item())
     assert err == 1, "the waiting rank must report the timeout"
     assert 40.0 < t0.elapsed_time(t1) < 2000.0  # bounded by timeout_ms, not by luck
-    # it still told 'rank 0' that it is done, so a live rank 0 would not wait for it forever
-    assert int(bufs[0][lay.off_ctrl + 8 : lay.off_ctrl + 12].view(torch.int32).item()) == 1
+
+
+def test_rank0_times_out_when_a_peer_never_delivers(shipped_inputs):
+    """The other direction: rank 0 of a world of two whose peer never runs. Rank 0 scores its own share,
+    then waits (bounded) for the peer's result rows and must come back with error word 2."""
+    import ctypes as C
+
+    import torch
+
+    from mpi_openmp_cuda_b200 import Problem
+    from mpi_openmp_cuda_b200.ops import _native as N
+    from mpi_openmp_cuda_b200.ops import plan
+    from mpi_openmp_cuda_b200.parallel.fabric import FabricDesc, FabricLayout
+
+    lib = N.cuda()
+    lib.sa_fabric_layout.argtypes = [C.c_uint32, C.c_size_t, C.POINTER(FabricLayout)]
+    lib.sa_cuda_fabric_solve.argtypes = [C.POINTER(FabricDesc), C.POINTER(N.BlobHeader), C.c_void_p]
+    blob = plan.plan_pack(Problem.from_file(shipped_inputs[3][0]), 2)
+    lay = FabricLayout()
+    N.check(lib.sa_fabric_layout(64, 1 << 20, C.byref(lay)))
+    bufs = [torch.zeros(int(lay.total_bytes), dtype=torch.uint8, device="cuda:0") for _ in range(2)]
+    bufs[0][lay.off_blob : lay.off_blob + blob.nbytes].copy_(torch.from_numpy(blob.numpy()[: blob.nbytes]))
+    d = FabricDesc()
+    d.rank, d.world, d.epoch, d.use_multicast, d.timeout_ms = 0, 2, 1, 0, 50
+    d.peer_base[0], d.peer_base[1] = bufs[0].data_ptr(), bufs[1].data_ptr()
+    d.layout = lay
+    t0 = torch.cuda.Event(enable_timing=True)
+    t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    N.check(lib.sa_cuda_fabric_solve(C.byref(d), C.byref(blob.header), None))
+    t1.record()
+    torch.cuda.synchronize()
+    err = int(bufs[0][lay.off_ctrl + 12 : lay.off_ctrl + 16].view(torch.int32).item())
+    assert err == 2, "rank 0 must report that rows never arrived"
+    assert 40.0 < t0.elapsed_time(t1) < 2000.0
+    # the header packet did reach the (absent) peer's buffer: epoch in the upper half of every word
+    pkt = bufs[1][lay.off_hdr_ll : lay.off_hdr_ll + 16].view(torch.int64).cpu().tolist()
+    assert pkt[0] >> 32 == 1 and (pkt[0] & 0xFFFFFFFF) == 0x31424153

@@ -214,7 +214,7 @@ def test_torch_ops_binding(solver, shipped_inputs):
     p = Problem.from_file(shipped_inputs[3][0])
     blob = plan.plan_pack(p)
     d_blob = torch.from_numpy(blob.numpy()[: blob.nbytes].copy()).cuda()
-    header = torch.from_numpy(blob.numpy()[:256].copy())
+    header = torch.from_numpy(blob.numpy()[:1024].copy())
     scratch = torch.zeros(int(ops.scratch_bytes(blob.nseq)), dtype=torch.uint8, device="cuda")
     for _ in range(2):
         out = ops.solve_blob(d_blob, header, scratch)

@@ -198,10 +198,15 @@ def test_stream_mode_partitions_whole_pairs_over_ranks():
     blob = plan.plan_pack(p, 4, mode="stream")
     assert blob.mode == "stream" and blob.header.world == 4
     h, tab, items = blob.header, blob.seq_table(), blob.items()
-    pairs = blob.numpy()[h.off_pairs : h.off_pairs + 8 * h.npairs].view(np.dtype([("a", "<u4"), ("b", "<u4")]))
+    pairs = blob.pair_records()
     loads = []
     for r in range(4):
         sl = items[h.rank_first_item[r] : h.rank_first_item[r + 1]]
+        # a rank's pairs are one contiguous slice of the record table, its letters one byte range
+        assert sl["seq"].min() == h.rank_first_pair[r] and sl["seq"].max() == h.rank_first_pair[r + 1] - 1
+        mine = pairs[h.rank_first_pair[r] : h.rank_first_pair[r + 1]]
+        assert mine["off_a"].min() >= h.rank_seq2_lo[r] and (mine["off_a"] + mine["crow"]).max() <= h.rank_seq2_hi[r]
+        assert np.all(mine["home"] == r)
         for pid in np.unique(sl["seq"]):
             a, b = int(pairs["a"][pid]), int(pairs["b"][pid])
             assert int(tab["home"][a]) == r and (b == 0xFFFFFFFF or int(tab["home"][b]) == r)
@@ -210,3 +215,55 @@ def test_stream_mode_partitions_whole_pairs_over_ranks():
     assert np.array_equal(plan.execute_blob_cpu(blob), solve_cpu(p, "fast"))
     with pytest.raises(NativeError):
         plan.plan_pack(p, 4, mode="pair")  # PAIR (CTA-per-pair) is single-GPU
+
+
+def _sparse_rank_walk(blob, world):
+    """Score every rank's items from a blob that holds ONLY that rank's ranges (sa_blob_rank_ranges),
+    max-reduce the keys, finalise on the full blob: what the fabric kernels / the CPU world do."""
+    import ctypes as C
+
+    from mpi_openmp_cuda_b200.ops import _native as N
+    from mpi_openmp_cuda_b200.parallel.cpu_world import rank_ranges
+
+    full = blob.numpy()[: blob.nbytes]
+    h = blob.header
+    keys = np.zeros(max(blob.nseq, 1), dtype=np.uint64)
+    moved = []
+    for r in range(world):
+        sparse = np.zeros(blob.nbytes, dtype=np.uint8)
+        sparse[:1024] = full[:1024]
+        rr = rank_ranges(h, r)
+        for a, b in rr:
+            sparse[a:b] = full[a:b]
+        moved.append(sum(b - a for a, b in rr))
+        mine = np.zeros_like(keys)
+        N.check(N.core().sa_blob_score_items_cpu(C.c_void_p(sparse.ctypes.data), blob.nbytes, int(h.rank_first_item[r]),
+                                                 int(h.rank_first_item[r + 1]), mine.ctypes.data_as(C.POINTER(C.c_uint64))))
+        keys = np.maximum(keys, mine)
+    out = np.zeros((max(blob.nseq, 1), 4), dtype=np.int32)
+    N.check(N.core().sa_blob_finalize_cpu(C.c_void_p(full.ctypes.data), blob.nbytes, keys.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                          out.ctypes.data_as(C.POINTER(C.c_int32))))
+    return out[: blob.nseq, :3], moved
+
+
+@pytest.mark.parametrize("mode", ["tile", "stream"])
+def test_each_rank_needs_only_its_own_ranges(mode):
+    p = random_problem(600, len1=700, len2_range=(20, 600), seed=11)
+    blob = plan.plan_pack(p, 4, mode=mode)
+    res, moved = _sparse_rank_walk(blob, 4)
+    assert np.array_equal(res, solve_cpu(p, "fast"))
+    # a scatter, not a broadcast: what the four ranks receive adds up to about one blob, not four
+    assert sum(moved) < 1.3 * blob.nbytes
+
+
+def test_split_tiles_deals_one_sequence_over_several_ranks(shipped_inputs):
+    p = Problem.from_file(shipped_inputs[3][0])
+    blob = plan.plan_pack(p, 4, mode="tile", split_tiles=True)
+    h, items = blob.header, blob.items()
+    owners = {}
+    for r in range(4):
+        for s in items[h.rank_first_item[r] : h.rank_first_item[r + 1]]["seq"]:
+            owners.setdefault(int(s), set()).add(r)
+    assert any(len(v) > 1 for v in owners.values()), "no sequence was split over ranks"
+    res, _ = _sparse_rank_walk(blob, 4)
+    assert np.array_equal(res, solve_cpu(p, "fast"))
