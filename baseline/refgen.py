@@ -2,8 +2,8 @@
 
 `bench.py --impl reference` must not load any native code of this repository, so everything the
 arm needs besides the reference binary itself lives here: the input grammar (main.c:76-108), the
-scaled-input generator (same bytes as `mpi_openmp_cuda_b200.models.synthetic.scaled_input3`, which
-is built on top of this module so that both bench arms read byte-identical input), the candidate
+scaled-input generator (byte-identical to `mpi_openmp_cuda_b200.models.synthetic.scaled_input3`,
+an independent implementation; tests/test_refgen.py holds the two together), the candidate
 count (cudaFunctions.cu:116-118) and a numpy restatement of the scoring contract
 used to count how many rows the reference binary gets right.
 """
@@ -90,7 +90,7 @@ def solve(weights, seq1: bytes, seqs):
     for s in seqs:
         s2 = np.frombuffer(s, dtype=np.uint8)
         m = len(s2)
-        if m > l1 or m == 0:
+        if m > l1 or (m == 0 and l1 > 0):
             res.append((INT_MIN, 0, 0))
             continue
         if m == l1:

@@ -62,6 +62,7 @@ Triple solve_one_fast(const int32_t w[4], const std::string& s1, const std::stri
     const int64_t l1 = (int64_t)s1.size(), l2 = (int64_t)s2.size();
     Triple best{INT_MIN, 0, 0};
     if (l2 > l1) return best;
+    if (l2 == 0 && l1 > 0) return best;  // an empty Seq2 has no (n,k) candidate at all (the k loop never runs)
     const PairValues val(w);
     auto diag_total = [&](int64_t n) {
         int64_t t = 0;

@@ -78,7 +78,7 @@ SeqPlan plan_sequence(uint32_t len1, uint32_t len2) {
     SeqPlan sp;
     sp.len = len2;
     sp.ndiag = (int32_t)len1 - (int32_t)len2;
-    if (sp.ndiag < 0) {  // no candidates (cudaFunctions.cu:116 loop never runs)
+    if (sp.ndiag < 0 || (len2 == 0 && len1 > 0)) {  // no candidates (cudaFunctions.cu:116-118 loops never run)
         sp.ntiles = 0;
         return sp;
     }
@@ -146,7 +146,7 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
             return SA_ERR_UNSUPPORTED;
         }
         max_len2 = std::max<uint32_t>(max_len2, (uint32_t)l2);
-        if (l2 <= len1) ++nvalid;
+        if (l2 <= len1 && (l2 > 0 || len1 == 0)) ++nvalid;
     }
 
     // ---- pair mode (two sequences per 32-bit lane as u16x2, per-pair profile in shared memory)
@@ -168,7 +168,7 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     std::vector<uint32_t> order;  // scorable sequences, longest first; neighbours become pairs
     if (pair_ok && want_pairs) {
         for (uint32_t s = 0; s < nseq; ++s)
-            if (p->seq2[s].size() <= len1) order.push_back(s);
+            if (p->seq2[s].size() <= len1 && (!p->seq2[s].empty() || len1 == 0)) order.push_back(s);
         std::stable_sort(order.begin(), order.end(),
                          [&](uint32_t x, uint32_t y) { return p->seq2[x].size() > p->seq2[y].size(); });
     }

@@ -62,6 +62,7 @@ struct KParams {
     unsigned long long timeout_ns;
     uint32_t timeline;  // 1: record the globaltimer timeline in the control block
     uint32_t skip_push; // 1: re-solve of the blob every rank already holds (resident re-solve)
+    uint32_t dbg_src;   // debug (SA_DEBUG_SRC): bit 0 read Seq2 letters, bit 1 read items/records from rank 0's copy instead of the staged one
 };
 
 // Words of the control block at the start of every rank's symmetric buffer (all local to the rank
@@ -258,6 +259,7 @@ __device__ __forceinline__ uint32_t pull_chunk_of(const PullPlan& pp, uint32_t j
 // the number of threads cooperating (a CTA in TILE mode, a warp in STREAM mode). The caller synchronises
 // the cooperating threads afterwards and lets ONE of them call pull_publish.
 __device__ __forceinline__ void pull_copy(const KParams& p, const sa_blob_header& h, uint32_t chunk, uint32_t t, uint32_t nt) {
+    if (p.dbg_src & 4u) return;  // debug: pretend-copy (flags and queue behave as usual, no bytes move)
     const uint32_t cb = h.chunk_bytes, base = chunk * cb;
     const uint32_t n16 = (min(cb, h.total_bytes - base) + 15u) >> 4;
     const int4* src = reinterpret_cast<const int4*>(p.peer[0] + p.off_blob + base);
@@ -410,7 +412,10 @@ __device__ __forceinline__ void launch_epilogue(const KParams& p) {
     unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
     if (kFabric && p.rank == 0 && s_abort == 0u) {
         collect_results(p, my_ctl);
-        if (p.timeline && tid == 0) atomicMax(&times[4], global_ns());
+        if (p.timeline) {
+            __syncthreads();  // every thread of this CTA has validated its rows
+            if (tid == 0) atomicMax(&times[4], global_ns());
+        }
     }
     if (tid == 0) {
         __threadfence();
@@ -951,8 +956,10 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const sa_seq_desc* const seqtab = reinterpret_cast<const sa_seq_desc*>(p.blob + hdr->off_seqtab);
-    const sa_item* const items = reinterpret_cast<const sa_item*>(p.blob + hdr->off_items);
-    const sa_pair_rec* const pairs = reinterpret_cast<const sa_pair_rec*>(p.blob + hdr->off_pairs);
+    const unsigned char* const desc_base = (kFabric && (p.dbg_src & 2u)) ? p.peer[0] + p.off_blob : p.blob;
+    const unsigned char* const code_base = (kFabric && (p.dbg_src & 1u)) ? p.peer[0] + p.off_blob : p.blob;
+    const sa_item* const items = reinterpret_cast<const sa_item*>(desc_base + hdr->off_items);
+    const sa_pair_rec* const pairs = reinterpret_cast<const sa_pair_rec*>(desc_base + hdr->off_pairs);
     const int vmin = hdr->value_min;
     const int len1 = (int)hdr->len1;
     constexpr uint32_t BIG = kBig;
@@ -1060,8 +1067,8 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
         const bool has_b = ib != SA_NO_SEQ;
         const int ndiag_a = len1 - (int)pr.len_a, ndiag_b = len1 - (int)pr.len_b;
         const uint32_t rows = pr.crow, n0 = tile * SA_DIAG_PER_WARP;
-        const unsigned char* const gA = p.blob + pr.off_a;
-        const unsigned char* const gB = p.blob + pr.off_b;
+        const unsigned char* const gA = code_base + pr.off_a;
+        const unsigned char* const gB = code_base + pr.off_b;
         unsigned long long* const keyA_p = (kFabric ? reinterpret_cast<unsigned long long*>(p.peer[pr.home] + p.off_key) : p.key) + ia;
         unsigned long long* const keyB_p = (kFabric ? reinterpret_cast<unsigned long long*>(p.peer[pr.home] + p.off_key) : p.key) + (has_b ? ib : ia);
         unsigned int* const cnt_p = (kFabric ? reinterpret_cast<unsigned int*>(p.peer[pr.home] + p.off_cnt) : p.cnt) + ia;
@@ -1596,11 +1603,28 @@ int sa_session_solve(sa_session* s, const sa_problem* prob, int32_t* out3) {
         blob_dev = s->d_blob;
     }
     int32_t* out_dev = reinterpret_cast<int32_t*>(s->direct_out ? s->h_out : s->d_out);
+    // The scratch is carved by the CURRENT nseq and is only correct while the whole buffer is zero between
+    // solves; a launch that did not run to completion leaves dirty words, so any failure re-zeroes it.
+    auto rezero = [&]() { cudaMemsetAsync(s->d_scratch, 0, sa_cuda_scratch_bytes((uint32_t)s->d_scratch_cap), s->stream); };
     rc = sa_cuda_solve_blob(blob_dev, h, out_dev, s->d_scratch, s->stream);
-    if (rc != SA_OK) return rc;
-    if (!s->direct_out)
-        SA_CUDA_TRY(cudaMemcpyAsync(s->h_out, s->d_out, nseq * sizeof(int4), cudaMemcpyDeviceToHost, s->stream));
-    SA_CUDA_TRY(cudaStreamSynchronize(s->stream));
+    if (rc != SA_OK) {
+        rezero();
+        return rc;
+    }
+    if (!s->direct_out) {
+        const cudaError_t e = cudaMemcpyAsync(s->h_out, s->d_out, nseq * sizeof(int4), cudaMemcpyDeviceToHost, s->stream);
+        if (e != cudaSuccess) {
+            rezero();
+            return fail(e, "cudaMemcpyAsync(results)");
+        }
+    }
+    {
+        const cudaError_t e = cudaStreamSynchronize(s->stream);
+        if (e != cudaSuccess) {
+            rezero();
+            return fail(e, "cudaStreamSynchronize");
+        }
+    }
     s->h2d_bytes = got;
     s->d2h_bytes = nseq * sizeof(int4);
     for (size_t i = 0; i < nseq; ++i) {
@@ -1708,6 +1732,8 @@ int sa_cuda_fabric_solve(const sa_fabric_desc* f, const sa_blob_header* header, 
     p.timeout_ns = (unsigned long long)(f->timeout_ms ? f->timeout_ms : 10000u) * 1000000ull;
     p.timeline = f->pad0 & 1u;
     p.skip_push = (f->pad0 >> 1) & 1u;
+    static const uint32_t env_dbg_src = [] { const char* e = std::getenv("SA_DEBUG_SRC"); return e ? (uint32_t)std::atoi(e) : 0u; }();
+    p.dbg_src = env_dbg_src;
     p.blob = p.peer[f->rank] + p.off_blob;
     p.write_empty = f->rank == 0 ? 1u : 0u;
     // Ranks other than 0 know nothing about the problem at launch time, so every rank launches the
@@ -1760,6 +1786,12 @@ void* g_static_scratch_addr[64] = {nullptr};
 int sa_cuda_solve_blob_noalloc(const void* d_blob, const sa_blob_header* header, int32_t* d_out, void* stream) {
     if (!d_blob || !header || !d_out) {
         sa_set_last_error("sa_cuda_solve_blob_noalloc: null argument");
+        return SA_ERR_ARG;
+    }
+    // Validate the header before anything is enqueued: a garbage header must not be reported as "too large",
+    // and nothing (not even the memset) may be launched for it.
+    if (header->magic != SA_BLOB_MAGIC || header->version != SA_BLOB_VERSION) {
+        sa_set_last_error("sa_cuda_solve_blob_noalloc: header is not a blob of this version");
         return SA_ERR_ARG;
     }
     if (header->nseq > SA_NOALLOC_MAX_SEQ) {

@@ -288,7 +288,7 @@ int sa_cuda_solve_problem(const sa_problem* p, int32_t* out, int device);
 #define SA_NOALLOC_MAX_SEQ 4096u
 
 /* Same solve as sa_cuda_solve_blob, for callers that cannot allocate device memory.
- * (No counterpart in the reference: it cudaMallocs per row, cudaFunctions.cu:189-206.)
+ * (No counterpart in the reference.)
  *
  * Meant for code that runs where HBM already belongs to someone else's pool — a plug-in or
  * custom op executing inside a server or framework that owns the allocator — or where the

@@ -12,6 +12,7 @@ from functools import lru_cache
 from ..utils import build as _build
 
 SA_OK = 0
+SA_ERR_ARG = 2
 SA_ERR_UNSUPPORTED = 3
 SA_ERR_TOO_LARGE = 6
 SA_ERR_SMALL_BUFFER = 7

@@ -267,3 +267,18 @@ def test_split_tiles_deals_one_sequence_over_several_ranks(shipped_inputs):
     assert any(len(v) > 1 for v in owners.values()), "no sequence was split over ranks"
     res, _ = _sparse_rank_walk(blob, 4)
     assert np.array_equal(res, solve_cpu(p, "fast"))
+
+
+@pytest.mark.parametrize("mode", ["tile", "pair", "stream"])
+def test_empty_sequence_has_no_candidates_in_every_layer(mode):
+    """An empty Seq2 (the parser cannot produce one, from_parts can) is a row without candidates:
+    (INT_MIN, 0, 0) from both oracles and from the walk of every mode, as for len2 > len1."""
+    seqs = ["", "HELLO", "", "WORLD", "HELLOWORLDHELLO"]
+    p = Problem.from_parts((5, 1, 2, 3), "HELLOWORLD", seqs)
+    naive, fast = solve_cpu(p, "naive"), solve_cpu(p, "fast")
+    assert np.array_equal(naive, fast)
+    assert naive[0].tolist() == [-2147483648, 0, 0] and naive[2].tolist() == [-2147483648, 0, 0]
+    assert p.candidates() == 5 * 5 * 2
+    blob = plan.plan_pack(p, mode=mode)
+    assert blob.seq_table()["ntiles"][0] == 0 and blob.seq_table()["ntiles"][2] == 0
+    assert np.array_equal(plan.execute_blob_cpu(blob), naive)
