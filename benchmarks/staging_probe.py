@@ -29,7 +29,7 @@ from mpi_openmp_cuda_b200.parallel.fabric import FabricDesc, FabricLayout  # noq
 from mpi_openmp_cuda_b200.utils.timing import L2Flusher  # noqa: E402
 
 NAMES = {1: "header_known", 17: "first_chunk_staged", 5: "all_chunks_staged", 2: "items_done", 16: "last_cta_exit",
-         8: "q1", 9: "q2", 10: "q3"}
+         8: "q1", 9: "q2", 10: "q3", 18: "first_warp_idle", 19: "last_warp_idle"}
 
 
 def main() -> int:
@@ -54,7 +54,7 @@ def main() -> int:
     d.rank, d.world, d.use_multicast, d.timeout_ms = 1, 2, 0, 2000
     d.peer_base[0], d.peer_base[1] = bufs[0].data_ptr(), bufs[1].data_ptr()
     d.layout = lay
-    tl = bufs[1][lay.off_ctrl + 64 : lay.off_ctrl + 64 + 8 * 18].view(torch.int64)
+    tl = bufs[1][lay.off_ctrl + 64 : lay.off_ctrl + 64 + 8 * 24].view(torch.int64)
     epoch = 0
 
     def run(resident: bool):
@@ -70,6 +70,7 @@ def main() -> int:
         tl.zero_()
         tl[0] = torch.iinfo(torch.int64).max
         tl[17] = torch.iinfo(torch.int64).max
+        tl[18] = torch.iinfo(torch.int64).max
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         N.check(lib.sa_cuda_fabric_solve(C.byref(d), None, None))
@@ -80,6 +81,8 @@ def main() -> int:
         err = int(bufs[1][lay.off_ctrl + 12 : lay.off_ctrl + 16].view(torch.int32).item())
         tlr = {n: (None if t[i] in (0, big) else round((t[i] - t[0]) / 1e3, 1)) for i, n in NAMES.items()}
         tlr["items_that_waited"], tlr["wait_us_total"] = t[6], round(t[7] / 1e3, 1)
+        tlr["longest_item_who"] = {"start_us": t[23] >> 40, "item": (t[23] >> 16) & 0xFFFFFF, "warp": (t[23] >> 8) & 0xFF, "odd_cta": (t[23] >> 1) & 1, "copied_before": t[23] & 1}
+        tlr["longest_item_us"], tlr["longest_item_last_quarter_us"], tlr["items_executed"], tlr["rows_walked"] = round(t[20] / 1e3, 1), round(t[21] / 1e3, 1), t[3], t[22]
         return e0.elapsed_time(e1) * 1e3, tlr, err
 
     out = {"config": f"input3 x{a.scale} per GPU, world 2, rank 1 alone on one GPU", "mode": blob.mode, "nseq": blob.nseq,

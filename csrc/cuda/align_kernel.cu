@@ -296,7 +296,12 @@ __device__ __forceinline__ bool wait_local_flag(const uint32_t* flag, uint32_t e
 
 // True when the blob bytes [lo, hi) are staged in this rank's buffer (always, on rank 0).
 // Fast path: the cached / single "all here" flag. Slow path: the flags of the covering chunks.
-__device__ __forceinline__ bool fabric_bytes_ready(const KParams& p, uint32_t* my_ctl, uint32_t lo, uint32_t hi) {
+// May be called by ONE thread (TILE: thread 0, the block barrier that follows re-joins the CTA) or by ALL
+// lanes of a warp with identical arguments (STREAM). A single lane of a warp must NOT call it on its own:
+// the wait loop is a divergent region that ptxas re-joins only at the end of the enclosing item, so the
+// warp then walks the whole item twice, once as lane 0 and once as lanes 1..31 (measured: the items that
+// had waited took 2x as long; ncu showed 29 active threads per instruction instead of 32).
+__device__ __forceinline__ bool fabric_bytes_ready(const KParams& p, uint32_t* my_ctl, uint32_t lo, uint32_t hi, bool leader = true) {
     volatile uint32_t* const cached = &s_all_here;
     if (*cached) return true;
     unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
@@ -310,7 +315,7 @@ __device__ __forceinline__ bool fabric_bytes_ready(const KParams& p, uint32_t* m
     for (uint32_t c = lo / cb; c <= (hi - 1u) / cb; ++c)
         if (!wait_local_flag(my_ctl + kCtlFlags + c, p.epoch, p.timeout_ns)) return false;
     __threadfence();  // one acquire fence for all the chunk flags just observed
-    if (p.timeline) {
+    if (p.timeline && leader) {
         atomicAdd(&times[6], 1ull);
         atomicAdd(&times[7], global_ns() - t0);
     }
@@ -1024,6 +1029,7 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
 
     uint32_t* const pw = prof + warp * (SA_STREAM_ROW_BLOCK * SA_ALPHABET);
     const uint32_t d0 = lane * kR;
+    unsigned long long dbg_copied = 0ull;
     for (;;) {
         uint32_t raw = 0;
         if (lane == 0) raw = atomicAdd(&my_ctl[kCtlNext], 1u);
@@ -1034,10 +1040,12 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
             pull_copy(p, *hdr, chunk, lane, 32u);
             __syncwarp();
             if (lane == 0) pull_publish(p, my_ctl, chunk, n_copy);
+            dbg_copied = 1u;
             continue;
         }
         if (raw - n_warp_copy >= item_end - item_begin) break;
         const uint32_t item = item_begin + (raw - n_warp_copy);
+        const unsigned long long t_item0 = (kFabric && p.timeline) ? global_ns() : 0ull;
         if (kFabric && p.timeline && lane == 0) {  // when were 25 / 50 / 75 % of this rank's items handed out?
             const uint32_t n_it = item_end - item_begin, k = item - item_begin;
             unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
@@ -1045,21 +1053,18 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
             if (k == n_it / 2) times[9] = global_ns();
             if (k == (n_it / 4) * 3) times[10] = global_ns();
         }
-        if (kFabric && p.rank != 0) {  // the item and its pair record may still be on their way
-            uint32_t ok = 1u;
-            if (lane == 0) {
-                const uint32_t io = hdr->off_items + 8u * item;
-                ok = fabric_bytes_ready(p, my_ctl, io, io + 8u) ? 1u : 0u;
-                if (ok) {
-                    const uint32_t po = hdr->off_pairs + 32u * items[item].seq;
-                    ok = fabric_bytes_ready(p, my_ctl, po, po + 32u) ? 1u : 0u;
-                }
-                if (!ok) {
-                    *reinterpret_cast<volatile uint32_t*>(&s_abort) = 1u;
-                    atomicExch(my_ctl + kCtlError, 1u);
-                }
+        if (kFabric && p.rank != 0) {  // the item and its pair record may still be on their way (warp-uniform wait)
+            const uint32_t io = hdr->off_items + 8u * item;
+            bool ok = fabric_bytes_ready(p, my_ctl, io, io + 8u, lane == 0);
+            if (ok) {
+                const uint32_t po = hdr->off_pairs + 32u * items[item].seq;
+                ok = fabric_bytes_ready(p, my_ctl, po, po + 32u, lane == 0);
             }
-            if (!__shfl_sync(0xFFFFFFFFu, ok, 0)) break;
+            if (!ok) {
+                *reinterpret_cast<volatile uint32_t*>(&s_abort) = 1u;
+                if (lane == 0) atomicExch(my_ctl + kCtlError, 1u);
+                break;
+            }
         }
         const uint32_t pid = items[item].seq, tile = items[item].tile;
         const sa_pair_rec pr = pairs[pid];
@@ -1072,17 +1077,14 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
         unsigned long long* const keyA_p = (kFabric ? reinterpret_cast<unsigned long long*>(p.peer[pr.home] + p.off_key) : p.key) + ia;
         unsigned long long* const keyB_p = (kFabric ? reinterpret_cast<unsigned long long*>(p.peer[pr.home] + p.off_key) : p.key) + (has_b ? ib : ia);
         unsigned int* const cnt_p = (kFabric ? reinterpret_cast<unsigned int*>(p.peer[pr.home] + p.off_cnt) : p.cnt) + ia;
-        if (kFabric && p.rank != 0) {  // the two sequences' letters may still be on their way
-            uint32_t ok = 1u;
-            if (lane == 0) {
-                ok = fabric_bytes_ready(p, my_ctl, pr.off_a, pr.off_a + rows) ? 1u : 0u;
-                if (ok && has_b) ok = fabric_bytes_ready(p, my_ctl, pr.off_b, pr.off_b + rows) ? 1u : 0u;
-                if (!ok) {
-                    *reinterpret_cast<volatile uint32_t*>(&s_abort) = 1u;
-                    atomicExch(my_ctl + kCtlError, 1u);
-                }
+        if (kFabric && p.rank != 0) {  // the two sequences' letters may still be on their way (warp-uniform wait)
+            bool ok = fabric_bytes_ready(p, my_ctl, pr.off_a, pr.off_a + rows, lane == 0);
+            if (ok && has_b) ok = fabric_bytes_ready(p, my_ctl, pr.off_b, pr.off_b + rows, lane == 0);
+            if (!ok) {
+                *reinterpret_cast<volatile uint32_t*>(&s_abort) = 1u;
+                if (lane == 0) atomicExch(my_ctl + kCtlError, 1u);
+                break;
             }
-            if (!__shfl_sync(0xFFFFFFFFu, ok, 0)) break;
         }
 
         uint32_t D[kR], best[kR], P8 = 0u;
@@ -1213,6 +1215,21 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
                 }
             }
         }
+        if (kFabric && p.timeline && lane == 0) {  // debug: longest item overall (20) and of the last quarter (21), ns
+            unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
+            const unsigned long long dt = global_ns() - t_item0;
+            if (atomicMax(&times[20], dt) < dt)  // (racy, debug only) who ran the longest item: start us | item | warp | did a copy before
+                times[23] = ((t_item0 - times[0]) / 1000ull) << 40 | (unsigned long long)(item - item_begin) << 16 | (unsigned long long)warp << 8 | (blockIdx.x & 1u) << 1 | dbg_copied;
+            if (item - item_begin >= ((item_end - item_begin) / 4u) * 3u) atomicMax(&times[21], dt);
+            atomicAdd(&times[3], 1ull);                          // items executed
+            atomicAdd(&times[22], (unsigned long long)rows);     // rows walked
+        }
+    }
+    if (kFabric && p.timeline && lane == 0) {  // debug: first (18) and last (19) warp to run out of items
+        unsigned long long* const times = reinterpret_cast<unsigned long long*>(my_ctl + kCtlTimes);
+        const unsigned long long t = global_ns();
+        atomicMin(&times[18], t);
+        atomicMax(&times[19], t);
     }
     __syncthreads();
     if (!epilogue_later) launch_epilogue<kFabric>(p);
@@ -1353,7 +1370,8 @@ int sa_cuda_solve_blob(const void* d_blob, const sa_blob_header* h, int32_t* d_o
                 di->smem_stream_set = (int)smem;
             }
         }
-        uint32_t grid = (uint32_t)di->sm_count * 2u;
+        static const uint32_t env_cps = [] { const char* e = std::getenv("SA_STREAM_CTAS_PER_SM"); return e ? (uint32_t)std::atoi(e) : 2u; }();
+        uint32_t grid = (uint32_t)di->sm_count * (env_cps == 1u ? 1u : 2u);
         const uint32_t need = (h->nitems + kWarps - 1u) / kWarps;
         if (need < grid) grid = need ? need : 1u;
         sa_score_stream_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
@@ -1749,7 +1767,8 @@ int sa_cuda_fabric_solve(const sa_fabric_desc* f, const sa_blob_header* header, 
             di->smem_fabric_set = (int)smem;
         }
     }
-    const uint32_t grid = (uint32_t)di->sm_count * 2u;
+    static const uint32_t env_cps = [] { const char* e = std::getenv("SA_STREAM_CTAS_PER_SM"); return e ? (uint32_t)std::atoi(e) : 2u; }();
+    const uint32_t grid = (uint32_t)di->sm_count * (env_cps == 1u ? 1u : 2u);
     static const sa_blob_header no_header{};  // ranks other than 0 receive the header through the fabric
     sa_score_fabric_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p, f->rank == 0 ? *header : no_header);
     SA_CUDA_TRY(cudaGetLastError());
