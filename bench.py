@@ -174,7 +174,10 @@ def run_ours(args):
             large_p = scaled_input3(args.large * n_gpus, ROOT / "data" / "input3.txt", seed=1)
         elif args.large:
             large_p = True  # other ranks only need to know that the phase exists
-        m = time_ours_distributed(problem, args.steps, args.warmup, large_p)
+        from mpi_openmp_cuda_b200 import Problem as _P
+
+        strong_p = _P.from_file(ROOT / "data" / args.input)  # every rank: only rank 0 uses more than its presence
+        m = time_ours_distributed(problem, args.steps, args.warmup, large_p, strong_p)
         if m is None:  # non-zero ranks print nothing
             return 0
     else:
@@ -235,6 +238,15 @@ def run_ours(args):
     if m.get("fabric"):
         line["fabric"] = m["fabric"]
         line["clocks_all_ranks"] = [{"sm_mhz": c.get("sm_mhz"), "reasons": c.get("reasons")} for c in m.get("clocks_all_ranks", [])]
+    if m.get("strong"):
+        st = m["strong"]
+        from mpi_openmp_cuda_b200 import Problem as _P
+
+        sp = _P.from_file(ROOT / "data" / args.input)
+        assert np.array_equal(st.pop("result"), solve_cpu(sp, "fast")), "strong-scaling config: GPU result differs from the CPU oracle"
+        st["config"] = f"{args.input} alone (strong scaling): its {st['items']} tiles dealt over {n_gpus} GPUs, cross-GPU argmax per split sequence"
+        st["candidates_per_s"] = sp.candidates() / (st["kernel_ms"] * 1e-3)
+        line["strong"] = st
     if m.get("large"):
         lg = m["large"]
         res_l = lg.pop("result")

@@ -38,7 +38,7 @@ def _max_over_ranks(ms: list[float]) -> list[float]:
     return [float(x) for x in t.cpu()]
 
 
-def time_ours_distributed(problem, steps: int, warmup: int, large_problem=None):
+def time_ours_distributed(problem, steps: int, warmup: int, large_problem=None, strong_problem=None):
     rank, world, local = init_distributed("nccl")
     # capacity handshake (bootstrap, outside any timed region): only rank 0 knows the problem
     need = torch.zeros(3, dtype=torch.int64, device="cuda")
@@ -174,6 +174,45 @@ def time_ours_distributed(problem, steps: int, warmup: int, large_problem=None):
         # put the headline problem back into rank 0's buffer for the final consistency check
         solver.launch_packed(blob)
         solver.fetch(nseq)
+    # ---- strong scaling of ONE shipped input: its tiles dealt over all GPUs, so single sequences are split
+    # and reduced with the cross-GPU argmax (atomicMax.sys on the home rank) — the reference's own mode of
+    # scaling (the same input3.txt over more ranks, main.c:110-119)
+    strong = None
+    if strong_problem is not None:
+        sblob = plan.plan_pack(strong_problem, world, mode="tile", split_tiles=True, out=solver._pinned_in(1 << 20)) if rank == 0 else None
+        s_n = torch.tensor([strong_problem.nseq if rank == 0 else 0], dtype=torch.int64, device="cuda")
+        dist.broadcast(s_n, 0)
+        solver.launch_packed(sblob)
+        sres = solver.fetch(int(s_n.item()))
+        sres = sres.copy() if rank == 0 else None
+        sms = []
+        for _ in range(max(5, min(steps, 20)) + 3):
+            torch.cuda.synchronize()
+            dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            flusher.flush()
+            align()
+            e0.record()
+            fabric.launch(sblob.header if rank == 0 else None)
+            e1.record()
+            e1.synchronize()
+            sms.append(e0.elapsed_time(e1))
+        sms = _max_over_ranks(sms[3:])
+        solver.check()
+        if rank == 0:
+            final_s = solver.fetch(int(s_n.item())).copy()
+            assert np.array_equal(final_s, sres), "strong-scaling results changed between steps"
+            it = sblob.items()
+            owners = {}
+            for r in range(world):
+                for q in it[sblob.header.rank_first_item[r]: sblob.header.rank_first_item[r + 1]]["seq"]:
+                    owners.setdefault(int(q), set()).add(r)
+            strong = {"kernel_ms": sum(sms) / len(sms), "kernel_ms_min": min(sms), "result": sres, "items": sblob.nitems,
+                      "sequences_split_over_gpus": sum(1 for v in owners.values() if len(v) > 1), "nseq": strong_problem.nseq}
+        else:
+            solver.fetch(0)
+        solver.launch_packed(blob)
+        solver.fetch(nseq)
     kernel_ms, e2e_ms, pre_ms = _max_over_ranks(kernel_ms), _max_over_ranks(e2e_ms), _max_over_ranks(pre_ms)
     total_launches = torch.tensor([launches], dtype=torch.int64, device="cuda")
     dist.all_reduce(total_launches)
@@ -189,6 +228,7 @@ def time_ours_distributed(problem, steps: int, warmup: int, large_problem=None):
         "padded_cells": int(blob.header.padded_cells), "nitems": blob.nitems,
         "fabric": {"multicast": fabric.use_multicast, "world": world},
         "large": large,
+        "strong": strong,
         "large_mode": lblob.mode if large is not None else None,
         "mode": blob.mode,
     }

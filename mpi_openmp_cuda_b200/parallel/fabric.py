@@ -44,6 +44,9 @@ def init_distributed(backend: str | None = None) -> tuple[int, int, int]:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29531")
         kw = {"device_id": torch.device("cuda", local)} if backend == "nccl" else {}
+        rdzv = os.environ.get("SA_RDZV_FILE")  # our launcher: a file-store rendezvous, no TCP port to collide on
+        if rdzv:
+            kw["init_method"] = f"file://{rdzv}"
         dist.init_process_group(backend, rank=rank, world_size=world, **kw)
     return rank, world, local
 

@@ -9,16 +9,10 @@ from __future__ import annotations
 import argparse
 import json
 import os
-import socket
 import subprocess
 import sys
+import tempfile
 import time
-
-
-def _free_port() -> int:
-    with socket.socket() as s:
-        s.bind(("127.0.0.1", 0))
-        return s.getsockname()[1]
 
 
 def worker(cpu: bool, timing_path: str | None) -> int:
@@ -70,12 +64,14 @@ def main() -> int:
         return worker(a.cpu, a.timing_json)
     data = sys.stdin.buffer.read()  # held by the parent so that a failed rendezvous can be retried
     rc = 1
-    for attempt in range(3):
-        port = _free_port()
+    for attempt in range(2):
+        # rendezvous through a fresh file store: no TCP port that another job could already hold
+        rdzv_dir = tempfile.mkdtemp(prefix="sa_rdzv_")
         procs = []
         for r in range(a.gpus):
             env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(a.gpus), LOCAL_RANK=str(r),
-                       MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+                       SA_RDZV_FILE=os.path.join(rdzv_dir, "store"))
+            env.pop("MASTER_PORT", None)
             cmd = [sys.executable, "-m", "mpi_openmp_cuda_b200.parallel.launcher", "--worker", "--gpus", str(a.gpus)]
             if a.cpu:
                 cmd.append("--cpu")

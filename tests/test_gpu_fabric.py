@@ -76,6 +76,22 @@ def test_two_gpus_stream_mode_through_the_fabric():
     assert b"stream fabric ok" in out.stdout
 
 
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_split_sequence_cross_gpu_argmax(world):
+    """One sequence's offset tiles on several GPUs: keys reduced with atomicMax.sys on the home rank,
+    finished by the last-arriving tile wherever it ran; ties, an exact substring, two solves in a row."""
+    if _ngpu() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import os
+
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
+                          "--master-addr", "127.0.0.1", "--master-port", str(29740 + world),
+                          str(ROOT / "tests" / "_fabric_split_worker.py")],
+                         capture_output=True, cwd=ROOT, timeout=600, env=dict(os.environ, PYTHONPATH=str(ROOT)))
+    assert out.returncode == 0, out.stderr.decode()[-3000:]
+    assert b"split fabric ok" in out.stdout
+
+
 def test_dead_peer_times_out_instead_of_hanging():
     """Fault injection for SURVEY.md 5.3 / R11: a rank whose peer never broadcasts must come back with
     an error word, not spin forever (the reference's exit(1) leaves its peers inside MPI collectives).
