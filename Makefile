@@ -17,7 +17,7 @@ CUDA_SRC := csrc/cuda/align_kernel.cu csrc/cuda/fabric_bench.cu
 CORE_LIB := $(LIBDIR)/libseqalign_core.so
 CUDA_LIB := $(LIBDIR)/libseqalign_cuda.so
 
-.PHONY: build core cuda clean run runOn2 test sass asan tsan microbench
+.PHONY: build core cuda clean run runOn2 test sass asan tsan microbench tc_scan
 
 build: core cuda final
 
@@ -42,6 +42,12 @@ microbench: build/microbench
 build/microbench: csrc/cuda/microbench.cu
 	@mkdir -p build
 	$(NVCC) -O3 -std=c++17 $(GENCODE) -lineinfo -o $@ $<
+
+# tcgen05 / TMEM variant of the scan as a stand-alone measured experiment: profiles/tc_scan.json
+tc_scan: build/tc_scan
+build/tc_scan: csrc/cuda/tc_scan.cu csrc/cuda/ptx_helpers.cuh
+	@mkdir -p build
+	$(NVCC) -O3 -std=c++17 $(GENCODE) -lineinfo -Xptxas -v -o $@ $<
 
 clean:
 	rm -f final $(LIBDIR)/*.so csrc/**/*.o
