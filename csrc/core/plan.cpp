@@ -102,6 +102,18 @@ SeqPlan plan_sequence(uint32_t len1, uint32_t len2) {
     return sp;
 }
 
+// dst[i] = src[i] & 31 (the code of an upper-case letter); returns non-zero when some byte is not 'A'..'Z'.
+// Restrict-qualified and branch-free so that the compiler vectorises it: this loop is the whole cost of packing.
+unsigned encode_letters(const unsigned char* __restrict src, unsigned char* __restrict dst, size_t n) {
+    unsigned char notletter = 0;
+    for (size_t i = 0; i < n; ++i) {
+        const unsigned char c = src[i];
+        dst[i] = (unsigned char)(c & 31u);
+        notletter |= (unsigned char)((unsigned char)(c - 'A') > 25u);
+    }
+    return notletter;
+}
+
 inline uint64_t pack_key(int32_t score, uint32_t n) {
     return ((uint64_t)((uint32_t)score ^ 0x80000000u) << 32) | (uint64_t)(0xFFFFFFFFu - n);
 }
@@ -291,21 +303,31 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
         auto steps = [](const SeqPlan& sp) { return (uint64_t)sp.crow + 2ull * (kWarps >> sp.wd_log2); };
         uint64_t nit = 0;
         for (uint32_t s = 0; s < nseq; ++s) nit += plans[s].ntiles;
-        while (nit < slots) {
-            uint32_t worst = nseq;
+        if (nit < slots) {
+            // longest item first: a max-heap over (steps, sequence)
+            std::vector<std::pair<uint64_t, uint32_t>> heap;
+            heap.reserve(nseq);
             for (uint32_t s = 0; s < nseq; ++s)
-                if (plans[s].ntiles && (worst == nseq || steps(plans[s]) > steps(plans[worst]))) worst = s;
-            if (worst == nseq || plans[worst].wd_log2 == 0) break;  // the longest item cannot be split further
-            SeqPlan sp = plans[worst];
-            sp.wd_log2 -= 1;
-            const uint32_t wr = kWarps >> sp.wd_log2, tn = kWarpDiag << sp.wd_log2;
-            const uint32_t d = sp.ndiag == 0 ? 1u : (uint32_t)sp.ndiag;
-            sp.crow = round_up((sp.len + wr - 1) / wr, kU);
-            sp.ntiles = (d + tn - 1) / tn;
-            sp.item_cost = (uint64_t)tn * wr * sp.crow;
-            if (steps(sp) >= steps(plans[worst]) || nit - plans[worst].ntiles + sp.ntiles > slots) break;
-            nit += sp.ntiles - plans[worst].ntiles;
-            plans[worst] = sp;
+                if (plans[s].ntiles) heap.emplace_back(steps(plans[s]), s);
+            std::make_heap(heap.begin(), heap.end());
+            while (nit < slots && !heap.empty()) {
+                std::pop_heap(heap.begin(), heap.end());
+                const uint32_t worst = heap.back().second;
+                heap.pop_back();
+                if (plans[worst].wd_log2 == 0) break;  // the longest item cannot be split further
+                SeqPlan sp = plans[worst];
+                sp.wd_log2 -= 1;
+                const uint32_t wr = kWarps >> sp.wd_log2, tn = kWarpDiag << sp.wd_log2;
+                const uint32_t d = sp.ndiag == 0 ? 1u : (uint32_t)sp.ndiag;
+                sp.crow = round_up((sp.len + wr - 1) / wr, kU);
+                sp.ntiles = (d + tn - 1) / tn;
+                sp.item_cost = (uint64_t)tn * wr * sp.crow;
+                if (steps(sp) >= steps(plans[worst]) || nit - plans[worst].ntiles + sp.ntiles > slots) break;
+                nit += sp.ntiles - plans[worst].ntiles;
+                plans[worst] = sp;
+                heap.emplace_back(steps(sp), worst);
+                std::push_heap(heap.begin(), heap.end());
+            }
         }
     }
     if (use_pairs) {
@@ -529,10 +551,17 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
                 tab[s].crow = (uint16_t)sp.crow;
                 const std::string& q = p->seq2[s];
                 unsigned char* dstq = base + seq_off[s];
-                for (size_t i = 0; i < q.size(); ++i) {
-                    const int c = al.code[(unsigned char)q[i]];
-                    bad |= c;
-                    dstq[i] = (unsigned char)c;
+                if (attempt == 0) {
+                    // letters-only first pass: the code of an upper-case letter is its low five bits; anything
+                    // else sets `bad` and triggers the table-driven refill (a branch-free loop the compiler vectorises)
+                    const unsigned notletter = encode_letters(reinterpret_cast<const unsigned char*>(q.data()), dstq, q.size());
+                    if (notletter) bad = -1;
+                } else {
+                    for (size_t i = 0; i < q.size(); ++i) {
+                        const int c = al.code[(unsigned char)q[i]];
+                        bad |= c;
+                        dstq[i] = (unsigned char)c;
+                    }
                 }
                 const size_t slot = round_up(std::max(sp.rows_padded(), (uint32_t)q.size()), 16);
                 std::memset(dstq + q.size(), 0, slot - q.size());

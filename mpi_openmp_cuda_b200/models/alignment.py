@@ -35,8 +35,11 @@ class AlignmentSolver:
 
     def pack(self, problem, mode: str = "auto") -> plan.PackedBlob:
         """Plan + pack straight into this solver's pinned staging buffer."""
-        need = plan.blob_size(problem, 1, mode)
-        return plan.plan_pack(problem, 1, out=self._pinned_in(need), mode=mode)
+        try:  # one pass into the staging buffer we already have; size + grow only when it is too small
+            return plan.plan_pack(problem, 1, out=self._pinned_in(1), mode=mode)
+        except ValueError:
+            need = plan.blob_size(problem, 1, mode)
+            return plan.plan_pack(problem, 1, out=self._pinned_in(need), mode=mode)
 
     def solve_packed(self, blob: plan.PackedBlob, sync: bool = True) -> np.ndarray:
         """H2D -> kernel -> D2H for an already packed problem. Returns int32[nseq,3]."""

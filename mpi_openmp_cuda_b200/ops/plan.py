@@ -82,22 +82,25 @@ def plan_pack(problem, world: int = 1, pinned: bool = False, out=None, mode: str
     code SA_ERR_UNSUPPORTED when the input is outside the GPU executor's limits.
     mode: 'auto' | 'tile' (any input) | 'pair' (u16x2 throughput mode, single GPU) | 'stream';
     split_tiles: deal TILE items tile by tile so that single sequences are split over GPUs."""
-    need = blob_size(problem, world, mode, split_tiles)
-    if out is not None:
-        buf = out
-        if buf.numel() < need:
-            raise ValueError("provided buffer too small")
-        ptr = buf.data_ptr()
-    elif pinned:
-        import torch
-
-        buf = torch.empty(need, dtype=torch.uint8, pin_memory=True)
-        ptr = buf.data_ptr()
-    else:
-        buf = np.empty(need, dtype=np.uint8)
-        ptr = buf.ctypes.data
     got = C.c_size_t()
-    N.check(N.core().sa_plan_pack_mode(problem.handle, world, _mode(mode, split_tiles), C.c_void_p(ptr), need, C.byref(got)))
+    if out is not None:
+        # one pass straight into the caller's (pinned) buffer; only a buffer that turns out too small costs a sizing pass
+        buf, ptr = out, out.data_ptr()
+        rc = N.core().sa_plan_pack_mode(problem.handle, world, _mode(mode, split_tiles), C.c_void_p(ptr), int(buf.numel()), C.byref(got))
+        if rc == N.SA_ERR_SMALL_BUFFER:
+            raise ValueError("provided buffer too small")
+        N.check(rc)
+    else:
+        need = blob_size(problem, world, mode, split_tiles)
+        if pinned:
+            import torch
+
+            buf = torch.empty(need, dtype=torch.uint8, pin_memory=True)
+            ptr = buf.data_ptr()
+        else:
+            buf = np.empty(need, dtype=np.uint8)
+            ptr = buf.ctypes.data
+        N.check(N.core().sa_plan_pack_mode(problem.handle, world, _mode(mode, split_tiles), C.c_void_p(ptr), need, C.byref(got)))
     hdr = N.BlobHeader.from_buffer_copy(C.string_at(ptr, C.sizeof(N.BlobHeader)))
     return PackedBlob(buf, int(got.value), hdr)
 

@@ -30,8 +30,11 @@ class DistributedSolver:
         return self._pin_in
 
     def pack(self, problem) -> plan.PackedBlob:
-        need = plan.blob_size(problem, self.fabric.world)
-        return plan.plan_pack(problem, self.fabric.world, out=self._pinned_in(need))
+        try:  # one pass into the staging buffer we already have; size + grow only when it is too small
+            return plan.plan_pack(problem, self.fabric.world, out=self._pinned_in(1))
+        except ValueError:
+            need = plan.blob_size(problem, self.fabric.world)
+            return plan.plan_pack(problem, self.fabric.world, out=self._pinned_in(need))
 
     def launch_packed(self, blob: plan.PackedBlob | None) -> None:
         """All ranks call this once per solve; only rank 0 passes a blob."""
