@@ -13,7 +13,7 @@ INPUT     ?= data/input1.txt
 GPUS      ?= 1
 
 CORE_SRC := csrc/core/problem.cpp csrc/core/oracle.cpp csrc/core/plan.cpp
-CUDA_SRC := csrc/cuda/align_kernel.cu csrc/cuda/fabric_bench.cu
+CUDA_SRC := csrc/cuda/align_kernel.cu csrc/cuda/fabric_bench.cu csrc/cuda/native_fabric.cu
 CORE_LIB := $(LIBDIR)/libseqalign_core.so
 CUDA_LIB := $(LIBDIR)/libseqalign_cuda.so
 
@@ -28,13 +28,13 @@ $(CORE_LIB): $(CORE_SRC) csrc/core/core.hpp include/seqalign.h
 	@mkdir -p $(LIBDIR)
 	$(CXX) $(CXXFLAGS) -shared -o $@ $(CORE_SRC)
 
-$(CUDA_LIB): $(CUDA_SRC) $(wildcard csrc/cuda/*.cuh) include/seqalign.h $(CORE_LIB)
+$(CUDA_LIB): $(CUDA_SRC) $(wildcard csrc/cuda/*.cuh) csrc/host/native_wire.h include/seqalign.h $(CORE_LIB)
 	@mkdir -p $(LIBDIR)
 	$(NVCC) $(NVCCFLAGS) -shared -o $@ $(CUDA_SRC) -L$(LIBDIR) -lseqalign_core -Xlinker -rpath -Xlinker '$$ORIGIN'
 
 # `final` keeps the reference's binary name and stdin->stdout contract (makefile:4,11).
-final: csrc/host/final_main.cpp $(CORE_LIB) $(CUDA_LIB)
-	$(CXX) $(CXXFLAGS) -o $@ csrc/host/final_main.cpp -L$(LIBDIR) -lseqalign_core -ldl \
+final: csrc/host/final_main.cpp csrc/host/native_launch.cpp csrc/host/native_wire.h $(CORE_LIB) $(CUDA_LIB)
+	$(CXX) $(CXXFLAGS) -o $@ csrc/host/final_main.cpp csrc/host/native_launch.cpp -L$(LIBDIR) -lseqalign_core -ldl \
 	    -Wl,-rpath,'$$ORIGIN/$(LIBDIR)'
 
 # Pipe-rate micro-benchmarks (LDS / IADD3 / IMAD / VIMNMX / tcgen05.ld): profiles/MEASURED_PIPES.json

@@ -7,8 +7,10 @@
 //   --cpu-oracle        score on the CPU (O(len1*len2) oracle) instead of the GPU
 //   --cpu-naive         score on the CPU with the literal O(len1*len2^2) restatement
 //   --threads T         CPU threads for the oracle paths (default: hardware concurrency)
-//   --gpus N            use N GPUs of this node (N > 1 re-executes through the Python
-//                       launcher, one process per GPU, fabric kernels over NVLink)
+//   --gpus N            use N GPUs of this node: N native worker processes (native_launch.cpp), one
+//                       per GPU, fabric kernels over NVLink; no Python, torch or NCCL involved
+//   --fabric            take the multi-process fabric path even with --gpus 1
+//   --python-launcher   bootstrap the N processes through the Python package (torch symmetric memory) instead
 //   --device D          CUDA device for the single-GPU path (default 0)
 //   --timing-json PATH  write wall/solve timings as one JSON object to PATH
 //
@@ -52,9 +54,12 @@ double now_s() {
 
 }  // namespace
 
+int sa_native_launch(const std::string& text, int gpus, const std::string& root, const std::string& timing_path, int threads);
+
 int main(int argc, char** argv) {
     enum Mode { kGpu, kCpuFast, kCpuNaive } mode = kGpu;
     int threads = 0, gpus = 1, device = 0;
+    bool force_fabric = false, python_launcher = false;
     std::string timing_path;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
@@ -70,10 +75,12 @@ int main(int argc, char** argv) {
         else if (a == "--threads") threads = std::atoi(need("--threads"));
         else if (a == "--gpus") gpus = std::atoi(need("--gpus"));
         else if (a == "--device") device = std::atoi(need("--device"));
+        else if (a == "--fabric") force_fabric = true;
+        else if (a == "--python-launcher") python_launcher = true;
         else if (a == "--timing-json") timing_path = need("--timing-json");
         else if (a == "-h" || a == "--help") {
             std::fprintf(stderr,
-                         "usage: final [--cpu-oracle|--cpu-naive] [--threads T] [--gpus N] [--device D] "
+                         "usage: final [--cpu-oracle|--cpu-naive] [--threads T] [--gpus N [--python-launcher]] [--fabric] [--device D] "
                          "[--timing-json PATH] < input.txt\n");
             return 0;
         } else {
@@ -82,8 +89,10 @@ int main(int argc, char** argv) {
         }
     }
 
+    if (mode == kGpu && (gpus > 1 || force_fabric) && !python_launcher)
+        return sa_native_launch(read_all(stdin), gpus, exe_dir(), timing_path, threads);
     if (mode == kGpu && gpus > 1) {
-        // One process per GPU is bootstrapped by the Python launcher (torch.distributed for the
+        // The same run bootstrapped by the Python package (torch.distributed + symmetric memory for the
         // handle exchange only); stdin/stdout pass straight through.
         const std::string root = exe_dir();
         const std::string g = std::to_string(gpus);
@@ -112,6 +121,11 @@ int main(int argc, char** argv) {
     const char* engine = "gpu";
     int rc = SA_OK;
     if (mode == kGpu) {
+        // Let the driver initialise only the GPU we use (on an 8-GPU node it otherwise sets up all eight).
+        if (!std::getenv("CUDA_VISIBLE_DEVICES")) {
+            setenv("CUDA_VISIBLE_DEVICES", std::to_string(device).c_str(), 1);
+            device = 0;
+        }
         const std::string lib = exe_dir() + "/mpi_openmp_cuda_b200/_lib/libseqalign_cuda.so";
         void* h = dlopen(lib.c_str(), RTLD_NOW | RTLD_LOCAL);
         typedef int (*solve_fn)(const sa_problem*, int32_t*, int);

@@ -379,6 +379,28 @@ int sa_cuda_fabric_solve(const sa_fabric_desc* f, const sa_blob_header* header, 
 int sa_cuda_fabric_bcast(const sa_fabric_desc* f, uint64_t bytes, int ctas, void* stream);
 int sa_cuda_fabric_argmax(const sa_fabric_desc* f, const void* d_keys, uint64_t nkeys, int ctas, void* stream);
 
+/* One worker of a native multi-process solve (`final --gpus N`; the reference's `mpiexec -np N ./final`,
+ * makefile:11, with MPI_Init's wire-up, main.c:62-64): allocates this rank's symmetric buffer with the
+ * CUDA virtual-memory API, trades POSIX descriptors of the buffers (and of one multicast object when
+ * the GPUs support it) with the other workers through the launcher's socket `sock`
+ * (csrc/host/native_wire.h), maps them, and runs sa_cuda_fabric_solve. No Python, torch or NCCL.
+ * Every worker passes the same world, max_seq, max_blob_bytes, timeout_ms, use_multicast and repeat. */
+typedef struct sa_native_args {
+    int rank, world, sock, device;
+    const void* blob;             /* rank 0: the problem packed for `world` GPUs; others: NULL        */
+    const sa_blob_header* header; /* rank 0: host copy of the blob's header; others: NULL             */
+    uint32_t max_seq;             /* capacity of the result table (>= nseq)                           */
+    size_t max_blob_bytes;        /* capacity of the blob area (>= total_bytes)                       */
+    int32_t* results;             /* rank 0: int32[4*nseq] (score, n, k, 0)                           */
+    uint32_t timeout_ms;          /* bound on every cross-GPU wait (0 = 10 s)                         */
+    int use_multicast;            /* 0 = peer stores only; otherwise multicast when every GPU can     */
+    int repeat;                   /* solves in a row (>= 1); kernel_ms is the fastest                 */
+    int used_multicast;           /* out */
+    float kernel_ms;              /* out: device time of this rank's kernel (CUDA events)             */
+    double times[4];              /* out: seconds since entry at: CUDA up, buffers mapped, ready to launch, results on the host */
+} sa_native_args;
+int sa_native_worker(sa_native_args* a);
+
 /* Number of kernel launches issued by this library in this process. */
 uint64_t sa_cuda_launch_count(void);
 
