@@ -17,7 +17,7 @@ CUDA_SRC := csrc/cuda/align_kernel.cu csrc/cuda/fabric_bench.cu csrc/cuda/native
 CORE_LIB := $(LIBDIR)/libseqalign_core.so
 CUDA_LIB := $(LIBDIR)/libseqalign_cuda.so
 
-.PHONY: build core cuda clean run runOn2 test sass asan tsan microbench tc_scan
+.PHONY: build core cuda clean run runOn2 test sass asan tsan microbench tc_scan startup_probe
 
 build: core cuda final
 
@@ -48,6 +48,12 @@ tc_scan: build/tc_scan
 build/tc_scan: csrc/cuda/tc_scan.cu csrc/cuda/ptx_helpers.cuh
 	@mkdir -p build
 	$(NVCC) -O3 -std=c++17 $(GENCODE) -lineinfo -Xptxas -v -o $@ $<
+
+# Cold-start breakdown of a CUDA process (driver init / context / module load): profiles/cold_start.txt
+startup_probe: build/startup_probe
+build/startup_probe: csrc/cuda/startup_probe.cu
+	@mkdir -p build
+	$(NVCC) -O3 -std=c++17 $(GENCODE) -o $@ $<
 
 clean:
 	rm -f final $(LIBDIR)/*.so csrc/**/*.o

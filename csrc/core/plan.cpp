@@ -17,11 +17,17 @@
 // diagonals — O(len1*len2) instead of the reference's O(len1*len2^2).
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <cstdio>
 #include <climits>
 #include <cstdlib>
 #include <cstring>
 #include <numeric>
 #include <thread>
+#include <pthread.h>
 
 #include "core.hpp"
 
@@ -45,21 +51,98 @@ constexpr uint32_t kMergeCellsTile = 3, kMergeCellsPair = 10;
 
 inline uint32_t round_up(uint32_t v, uint32_t m) { return (v + m - 1) / m * m; }
 
-// Static split of [0, n) over host threads when the job is big enough to pay for them (the
-// reference's only OpenMP use is also input preparation, main.c:82,96 — there it races on stdin).
+// Host threads for the packer's bulk loops (the reference's only OpenMP use is also input preparation,
+// main.c:82,96 — there it races on stdin). The workers are started once and parked on a condition
+// variable: a large batch is packed range by range (sa_plan_pack_range), and starting 15 threads per range
+// would cost more than the range's share of the work.
+class Pool {
+   public:
+    static Pool* get() {
+        static std::once_flag once;
+        std::call_once(once, [] { pthread_atfork(nullptr, nullptr, [] { instance().store(nullptr); }); });
+        Pool* p = instance().load(std::memory_order_acquire);
+        if (!p) {
+            static std::mutex make;
+            std::lock_guard<std::mutex> g(make);
+            p = instance().load(std::memory_order_acquire);
+            if (!p) {
+                p = new Pool(std::min(16u, std::max(1u, std::thread::hardware_concurrency())));  // never freed: workers outlive main()
+                instance().store(p, std::memory_order_release);
+            }
+        }
+        return p;
+    }
+    unsigned size() const { return nworkers_ + 1; }
+    // fn(t) for t in [0, nt), t = 0 on the calling thread; false when another caller holds the pool
+    template <typename F>
+    bool run(unsigned nt, F&& fn) {
+        std::unique_lock<std::mutex> busy(busy_, std::try_to_lock);
+        if (!busy.owns_lock()) return false;
+        {
+            std::lock_guard<std::mutex> g(m_);
+            job_ = [&fn](unsigned t) { fn(t); };
+            want_ = nt - 1;
+            pending_ = nt - 1;
+            ++gen_;
+        }
+        wake_.notify_all();
+        fn(0u);
+        std::unique_lock<std::mutex> g(m_);
+        done_.wait(g, [&] { return pending_ == 0; });
+        job_ = nullptr;
+        return true;
+    }
+
+   private:
+    static std::atomic<Pool*>& instance() {
+        static std::atomic<Pool*> p{nullptr};
+        return p;
+    }
+    explicit Pool(unsigned n) : nworkers_(n > 1 ? n - 1 : 0) {
+        for (unsigned i = 0; i < nworkers_; ++i) std::thread([this, i] { loop(i + 1); }).detach();
+    }
+    void loop(unsigned id) {
+        unsigned seen = 0;
+        for (;;) {
+            std::function<void(unsigned)> job;
+            {
+                std::unique_lock<std::mutex> g(m_);
+                wake_.wait(g, [&] { return gen_ != seen; });
+                seen = gen_;
+                if (id > want_) continue;  // this job uses fewer threads
+                job = job_;
+            }
+            job(id);
+            {
+                std::lock_guard<std::mutex> g(m_);
+                if (--pending_ == 0) done_.notify_one();
+            }
+        }
+    }
+    const unsigned nworkers_;
+    std::mutex m_, busy_;
+    std::condition_variable wake_, done_;
+    std::function<void(unsigned)> job_;
+    unsigned gen_ = 0, want_ = 0, pending_ = 0;
+};
+
+// Static split of [0, n) over host threads when the job is big enough to pay for them.
 template <typename F>
 void parallel_for(uint32_t n, uint64_t work_bytes, F fn) {
-    unsigned nt = work_bytes < (4u << 20) ? 1u : std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+    unsigned nt = work_bytes < (1u << 20) ? 1u : Pool::get()->size();
     if (nt > n) nt = n ? n : 1u;
     if (nt <= 1) {
         fn(0u, n);
         return;
     }
-    std::vector<std::thread> pool;
-    for (unsigned t = 0; t < nt; ++t) {
+    auto part = [&](unsigned t) {
         const uint32_t a = (uint32_t)((uint64_t)n * t / nt), b = (uint32_t)((uint64_t)n * (t + 1) / nt);
-        pool.emplace_back([=]() { fn(a, b); });
-    }
+        fn(a, b);
+    };
+    static const bool no_pool = std::getenv("SA_PACK_POOL") && std::getenv("SA_PACK_POOL")[0] == '0';  // A/B switch
+    if (!no_pool && Pool::get()->run(nt, part)) return;
+    std::vector<std::thread> pool;  // the parked workers are busy with another caller's job
+    for (unsigned t = 0; t < nt; ++t) pool.emplace_back([&part, t]() { part(t); });
     for (auto& th : pool) th.join();
 }
 
@@ -125,16 +208,30 @@ extern "C" {
 
 // mode: SA_MODE_AUTO picks SA_MODE_PAIR for large single-GPU batches when its limits hold,
 // SA_MODE_TILE otherwise. Forcing SA_MODE_PAIR on an input outside its limits is an error.
-int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_t cap, size_t* blob_bytes) {
+// Plans and packs sequences [first, first + count) of the problem (their result rows are 0..count-1 of the
+// launch). The whole problem is the range [0, nseq); large batches are packed range by range so that
+// packing one range overlaps the copy and the kernel of the previous one (sa_session_solve).
+int sa_plan_pack_range(const sa_problem* p, uint32_t first, uint32_t count, int world, int mode, void* dst, size_t cap, size_t* blob_bytes) {
     using namespace sa;
     const bool split_flag = (mode & SA_MODE_SPLIT_TILES) != 0;
     mode &= ~SA_MODE_SPLIT_TILES;
-    if (!p || !blob_bytes || world < 1 || world > SA_MAX_WORLD || mode < SA_MODE_AUTO || mode > SA_MODE_STREAM) {
+    if (!p || !blob_bytes || world < 1 || world > SA_MAX_WORLD || mode < SA_MODE_AUTO || mode > SA_MODE_STREAM ||
+        (uint64_t)first + count > p->seq2.size()) {
         set_error("sa_plan_pack: bad argument");
         return SA_ERR_ARG;
     }
     const uint32_t len1 = (uint32_t)p->seq1.size();
-    const uint32_t nseq = (uint32_t)p->seq2.size();
+    const uint32_t nseq = count;
+    const std::string* const seq2 = p->seq2.data() + first;
+    // SA_PACK_TIMING=1: phase times of this call on stderr (profiling aid; see benchmarks/pack_phases.py)
+    static const bool timing = std::getenv("SA_PACK_TIMING") != nullptr;
+    auto t_prev = std::chrono::steady_clock::now();
+    auto mark = [&](const char* what) {
+        if (!timing || !dst) return;
+        const auto t = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "pack %-10s %8.1f us\n", what, std::chrono::duration<double, std::micro>(t - t_prev).count());
+        t_prev = t;
+    };
     if (p->seq1.size() > SA_GPU_MAX_SEQ1) {
         set_error("Seq1 longer than the GPU executor supports");
         return SA_ERR_UNSUPPORTED;
@@ -146,8 +243,10 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     // (build_alphabet) and a refill. Saves a pass over every byte on the latency-critical path.
     Alphabet al = letters_only_alphabet();
     uint32_t max_len2 = 0, nvalid = 0;
+    std::vector<uint32_t> len2(nseq);  // the planning passes below walk this array, not the strings
     for (uint32_t s = 0; s < nseq; ++s) {
-        const size_t l2 = p->seq2[s].size();
+        const size_t l2 = seq2[s].size();
+        len2[s] = (uint32_t)l2;
         if (l2 > SA_GPU_MAX_SEQ2) {
             set_error("a Seq2 is longer than the GPU executor supports");
             return SA_ERR_UNSUPPORTED;
@@ -179,21 +278,27 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     std::string stream_why = pair_why;
     std::vector<uint32_t> order;  // scorable sequences, longest first; neighbours become pairs
     if (pair_ok && want_pairs) {
+        // stable counting sort by length, longest first (lengths are bounded by SA_GPU_MAX_SEQ2)
+        std::vector<uint32_t> start((size_t)max_len2 + 2, 0);
+        auto scorable = [&](uint32_t s) { return len2[s] <= len1 && (len2[s] > 0 || len1 == 0); };
         for (uint32_t s = 0; s < nseq; ++s)
-            if (p->seq2[s].size() <= len1 && (!p->seq2[s].empty() || len1 == 0)) order.push_back(s);
-        std::stable_sort(order.begin(), order.end(),
-                         [&](uint32_t x, uint32_t y) { return p->seq2[x].size() > p->seq2[y].size(); });
+            if (scorable(s)) ++start[(size_t)(max_len2 - len2[s]) + 1];
+        for (size_t i = 1; i < start.size(); ++i) start[i] += start[i - 1];
+        order.resize(start.back());
+        for (uint32_t s = 0; s < nseq; ++s)
+            if (scorable(s)) order[start[(size_t)(max_len2 - len2[s])]++] = s;
     }
     // Fills `pairs` with the STREAM (one warp per tile, all rows) or PAIR (CTA per pair) geometry.
     auto plan_pairs = [&](bool as_stream, std::string& why) -> bool {
         pairs.clear();
+        pairs.reserve(order.size() / 2 + 1);
         pair_cols_needed = 0;
         for (size_t i = 0; i < order.size(); i += 2) {
             Pair pr;
             pr.a = order[i];
             pr.b = i + 1 < order.size() ? order[i + 1] : SA_NO_SEQ;
-            const uint32_t ma = (uint32_t)p->seq2[pr.a].size();
-            const uint32_t mb = pr.b == SA_NO_SEQ ? ma : (uint32_t)p->seq2[pr.b].size();
+            const uint32_t ma = len2[pr.a];
+            const uint32_t mb = pr.b == SA_NO_SEQ ? ma : len2[pr.b];
             const uint32_t rows = std::max(ma, mb), dmax = len1 - std::min(ma, mb);
             SeqPlan g;
             g.len = rows;
@@ -283,14 +388,21 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     }
     const bool use_pairs = pair_ok && mode != SA_MODE_TILE;
     const bool use_stream = use_pairs && stream_ok;
+    mark("pairs");
 
     // ---- per-sequence plans
     std::vector<SeqPlan> plans(nseq);
     uint32_t max_rows = kU, max_window = 16;
     uint64_t total_cells = 0, padded_cells = 0, nitems64 = 0;
     for (uint32_t s = 0; s < nseq; ++s) {
-        plans[s] = plan_sequence(len1, (uint32_t)p->seq2[s].size());
-        total_cells += (uint64_t)sa_problem_candidates(p, (int32_t)s);
+        if (use_pairs) {  // the pair's geometry replaces the sequence's own below: only len / ndiag are kept
+            plans[s].len = len2[s];
+            plans[s].ndiag = (int32_t)len1 - (int32_t)len2[s];
+            plans[s].ntiles = 0;
+        } else {
+            plans[s] = plan_sequence(len1, len2[s]);
+        }
+        total_cells += len2[s] > len1 ? 0u : len2[s] == len1 ? 1u : (uint64_t)(len1 - len2[s]) * len2[s];
     }
     if (!use_pairs) {
         // Latency mode. plan_sequence minimises each sequence's TOTAL padded cost, which is right when
@@ -359,6 +471,7 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
         return SA_ERR_UNSUPPORTED;
     }
     const uint32_t nitems = (uint32_t)nitems64;
+    mark("plans");
 
     // ---- partition: deal sequences (or tiles, when sequences are scarce) to ranks
     struct RankItem {
@@ -371,7 +484,10 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
     // SA_SPLIT_TILES=1 forces the per-tile deal (tests and the strong-scaling benchmark line)
     static const bool split_env = [] { const char* e = std::getenv("SA_SPLIT_TILES"); return e && *e && *e != '0'; }();
     if (use_pairs) {
-        std::stable_sort(pairs.begin(), pairs.end(), [](const Pair& x, const Pair& y) { return x.g.item_cost > y.g.item_cost; });
+        // STREAM: a tile costs 256 x crow and the pairs were formed longest first, so they already are
+        // costliest first; PAIR geometries differ per pair and need the sort
+        if (!use_stream)
+            std::stable_sort(pairs.begin(), pairs.end(), [](const Pair& x, const Pair& y) { return x.g.item_cost > y.g.item_cost; });
         if (use_stream) {
             // whole pairs are dealt to the least-loaded rank, costliest first: every atomic stays local
             std::vector<uint64_t> load((size_t)world, 0);
@@ -388,6 +504,7 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
             grouped.reserve(pairs.size());
             for (int r = 0; r < world; ++r) {
                 rank_first_pair[(size_t)r] = (uint32_t)grouped.size();
+                per_rank[(size_t)r].reserve((size_t)(nitems / (uint32_t)world) + 64);
                 for (uint32_t pid = 0; pid < pairs.size(); ++pid) {
                     if (pair_rank[pid] != r) continue;
                     const uint32_t nid = (uint32_t)grouped.size();
@@ -427,6 +544,7 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
         }
     }
 
+    mark("partition");
     // ---- layout
     uint32_t len1_padded = round_up(len1 + SA_SEQ1_TAIL_PAD, 16);
     if (use_pairs) len1_padded = std::max(len1_padded, round_up(pair_cols_needed + 16u, 16));
@@ -476,7 +594,7 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
         seq2_lo[(size_t)r] = (uint32_t)off;
         for (uint32_t s : group[(size_t)r]) {
             seq_off[s] = (uint32_t)off;
-            off += round_up(std::max(plans[s].rows_padded(), (uint32_t)p->seq2[s].size()), 16);
+            off += round_up(std::max(plans[s].rows_padded(), len2[s]), 16);
             if (off >= 0xFFFFF000ull) {
                 set_error("blob larger than 4 GiB");
                 return SA_ERR_UNSUPPORTED;
@@ -494,6 +612,7 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
         return SA_ERR_SMALL_BUFFER;
     }
 
+    mark("layout");
     // ---- fill
     unsigned char* base = static_cast<unsigned char*>(dst);
     std::memset(base, 0, off_seq2);  // header + tables + Seq1; every Seq2 slot zeroes its own padding below
@@ -549,7 +668,7 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
                 tab[s].wd_log2 = (uint8_t)sp.wd_log2;
                 tab[s].home = home[s];
                 tab[s].crow = (uint16_t)sp.crow;
-                const std::string& q = p->seq2[s];
+                const std::string& q = seq2[s];
                 unsigned char* dstq = base + seq_off[s];
                 if (attempt == 0) {
                     // letters-only first pass: the code of an upper-case letter is its low five bits; anything
@@ -576,6 +695,7 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
             return SA_ERR_UNSUPPORTED;
         }
     }
+    mark("letters");
     sa_item* items = reinterpret_cast<sa_item*>(base + off_items);
     uint32_t w = 0;
     for (int r = 0; r < world; ++r) {
@@ -622,7 +742,16 @@ int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_
             fat[i].home = d.home;
         }
     }
+    mark("records");
     return SA_OK;
+}
+
+int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_t cap, size_t* blob_bytes) {
+    if (!p) {
+        sa::set_error("sa_plan_pack: bad argument");
+        return SA_ERR_ARG;
+    }
+    return sa_plan_pack_range(p, 0, (uint32_t)p->seq2.size(), world, mode, dst, cap, blob_bytes);
 }
 
 int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, size_t* blob_bytes) {

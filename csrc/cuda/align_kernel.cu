@@ -1506,6 +1506,10 @@ struct sa_session {
     uint64_t h2d_bytes = 0, d2h_bytes = 0;
     size_t zero_copy_max = 0;          // blobs up to this size are read in place from pinned memory (measured slower: off)
     bool direct_out = true;            // result rows are written straight into pinned memory
+    size_t pipe_min_seq = 16384;       // batches at least this large are packed and launched in ranges of >= half of it
+                                       // (8192 sequences keep a range above AUTO's threshold for the STREAM kernel)
+    cudaEvent_t half_free[2] = {nullptr, nullptr};  // pipelined path: the H2D copy out of each half of h_in has finished
+    uint32_t last_launches = 0;
 };
 
 int sa_session_create(int device, sa_session** out) {
@@ -1517,6 +1521,7 @@ int sa_session_create(int device, sa_session** out) {
     sa_session* s = new (std::nothrow) sa_session();
     if (!s) return SA_ERR_NOMEM;
     s->device = device;
+    if (const char* v = std::getenv("SA_PIPE_MIN_SEQ")) s->pipe_min_seq = (size_t)std::atoll(v);  // 0 = never pipeline
     cudaError_t e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) {
         delete s;
@@ -1535,6 +1540,8 @@ void sa_session_destroy(sa_session* s) {
     cudaFree(s->d_blob);
     cudaFree(s->d_out);
     cudaFree(s->d_scratch);
+    for (cudaEvent_t e : s->half_free)
+        if (e) cudaEventDestroy(e);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
 }
@@ -1585,6 +1592,92 @@ int session_reserve(sa_session* s, size_t blob_bytes, size_t nseq) {
     }
     return SA_OK;
 }
+
+// Large batches: the host needs longer to pack the problem than the GPU needs to score it (input3 x 1024:
+// 4.3 ms against 1.3 ms on a B200 box), so the batch is cut into ranges of sequences and range k+1 is planned
+// and packed while range k is copied and scored. Two halves of the pinned and of the device buffer
+// alternate; everything runs in order on the session's stream, so the self-cleaning scratch is shared.
+int session_solve_pipelined(sa_session* s, const sa_problem* prob, int32_t* out3, size_t nseq) {
+    const size_t nranges = std::min<size_t>(8, std::max<size_t>(2, nseq / std::max<size_t>(1, s->pipe_min_seq / 2)));
+    for (cudaEvent_t& e : s->half_free)
+        if (!e) SA_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    int rc = session_reserve(s, s->h_in_cap, nseq);  // result table and scratch for the whole batch
+    if (rc != SA_OK) return rc;
+    auto rezero = [&]() {
+        cudaStreamSynchronize(s->stream);
+        cudaMemsetAsync(s->d_scratch, 0, sa_cuda_scratch_bytes((uint32_t)s->d_scratch_cap), s->stream);
+    };
+    int32_t* const out_dev = reinterpret_cast<int32_t*>(s->direct_out ? s->h_out : s->d_out);
+    uint64_t h2d = 0;
+    bool half_used[2] = {false, false};
+    s->last_launches = 0;
+    for (size_t k = 0; k < nranges; ++k) {
+        const uint32_t first = (uint32_t)(nseq * k / nranges), count = (uint32_t)(nseq * (k + 1) / nranges) - first;
+        const int half = (int)(k & 1);
+        size_t got = 0;
+        for (int attempt = 0;; ++attempt) {
+            const size_t half_cap = s->h_in_cap / 2 & ~(size_t)255;
+            if (half_used[half]) {
+                const cudaError_t e = cudaEventSynchronize(s->half_free[half]);  // its previous copy has left the pinned half
+                if (e != cudaSuccess) return fail(e, "cudaEventSynchronize");
+            }
+            rc = half_cap ? sa_plan_pack_range(prob, first, count, 1, SA_MODE_AUTO, s->h_in + half * half_cap, half_cap, &got) : SA_ERR_SMALL_BUFFER;
+            if (rc == SA_ERR_SMALL_BUFFER && attempt == 0) {
+                if (!half_cap) {
+                    rc = sa_plan_pack_range(prob, first, count, 1, SA_MODE_AUTO, nullptr, 0, &got);
+                    if (rc != SA_OK) return rc;
+                }
+                // growing the buffers frees them: nothing may be in flight
+                const cudaError_t e = cudaStreamSynchronize(s->stream);
+                if (e != cudaSuccess) return fail(e, "cudaStreamSynchronize");
+                half_used[0] = half_used[1] = false;
+                rc = session_reserve(s, 2 * (got + got / 4 + 256), nseq);
+                if (rc != SA_OK) return rc;
+                continue;
+            }
+            break;
+        }
+        if (rc != SA_OK) {
+            rezero();
+            return rc;  // SA_ERR_UNSUPPORTED: the caller falls back to the CPU for the whole batch
+        }
+        const size_t half_cap = s->h_in_cap / 2 & ~(size_t)255, dev_half = s->d_blob_cap / 2 & ~(size_t)255;
+        const unsigned char* h_blob = s->h_in + half * half_cap;
+        unsigned char* d_blob = s->d_blob + half * dev_half;
+        cudaError_t e = cudaMemcpyAsync(d_blob, h_blob, got, cudaMemcpyHostToDevice, s->stream);
+        if (e == cudaSuccess) e = cudaEventRecord(s->half_free[half], s->stream);
+        if (e != cudaSuccess) {
+            rezero();
+            return fail(e, "cudaMemcpyAsync(range)");
+        }
+        half_used[half] = true;
+        h2d += got;
+        const sa_blob_header* h = reinterpret_cast<const sa_blob_header*>(h_blob);  // read at launch time only
+        if (h->nseq) {
+            rc = sa_cuda_solve_blob(d_blob, h, out_dev + 4 * (size_t)first, s->d_scratch, s->stream);
+            if (rc != SA_OK) {
+                rezero();
+                return rc;
+            }
+            ++s->last_launches;
+        }
+    }
+    cudaError_t e = cudaSuccess;
+    if (!s->direct_out) e = cudaMemcpyAsync(s->h_out, s->d_out, nseq * sizeof(int4), cudaMemcpyDeviceToHost, s->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+    if (e != cudaSuccess) {
+        rezero();
+        return fail(e, "cudaStreamSynchronize");
+    }
+    s->h2d_bytes = h2d;
+    s->d2h_bytes = nseq * sizeof(int4);
+    for (size_t i = 0; i < nseq; ++i) {
+        out3[3 * i] = s->h_out[i].x;
+        out3[3 * i + 1] = s->h_out[i].y;
+        out3[3 * i + 2] = s->h_out[i].z;
+    }
+    return SA_OK;
+}
 }  // namespace
 
 int sa_session_solve(sa_session* s, const sa_problem* prob, int32_t* out3) {
@@ -1595,6 +1688,8 @@ int sa_session_solve(sa_session* s, const sa_problem* prob, int32_t* out3) {
     SA_CUDA_TRY(cudaSetDevice(s->device));
     const size_t nseq = (size_t)sa_problem_nseq(prob);
     if (nseq == 0) return SA_OK;
+    if (s->pipe_min_seq && nseq >= s->pipe_min_seq) return session_solve_pipelined(s, prob, out3, nseq);
+    s->last_launches = 1;
     // plan + pack once, straight into the pinned buffer; only a buffer that turns out too small
     // costs a second pass
     size_t got = 0;
@@ -1658,6 +1753,12 @@ void sa_session_configure(sa_session* s, size_t zero_copy_max_bytes, int direct_
     s->zero_copy_max = zero_copy_max_bytes;
     s->direct_out = direct_out != 0;
 }
+
+void sa_session_set_pipeline(sa_session* s, size_t min_seq) {
+    if (s) s->pipe_min_seq = min_seq;
+}
+
+uint32_t sa_session_last_launches(const sa_session* s) { return s ? s->last_launches : 0; }
 
 void sa_session_last_bytes(const sa_session* s, uint64_t* h2d, uint64_t* d2h) {
     if (h2d) *h2d = s ? s->h2d_bytes : 0;

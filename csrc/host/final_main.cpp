@@ -121,10 +121,29 @@ int main(int argc, char** argv) {
     const char* engine = "gpu";
     int rc = SA_OK;
     if (mode == kGpu) {
-        // Let the driver initialise only the GPU we use (on an 8-GPU node it otherwise sets up all eight).
-        if (!std::getenv("CUDA_VISIBLE_DEVICES")) {
-            setenv("CUDA_VISIBLE_DEVICES", std::to_string(device).c_str(), 1);
-            device = 0;
+        // Let the driver initialise only the GPU we use: on a multi-GPU node it otherwise sets up every visible
+        // device (measured: 0.73 s of driver start-up with one visible B200, 1.7-2.0 s with two).
+        {
+            std::vector<std::string> names;
+            if (const char* v = std::getenv("CUDA_VISIBLE_DEVICES")) {
+                std::string cur;
+                for (const char* c = v;; ++c) {
+                    if (*c == ',' || *c == 0) {
+                        if (!cur.empty()) names.push_back(cur);
+                        cur.clear();
+                        if (*c == 0) break;
+                    } else {
+                        cur.push_back(*c);
+                    }
+                }
+                if (device >= 0 && device < (int)names.size()) {
+                    setenv("CUDA_VISIBLE_DEVICES", names[(size_t)device].c_str(), 1);
+                    device = 0;
+                }
+            } else {
+                setenv("CUDA_VISIBLE_DEVICES", std::to_string(device).c_str(), 1);
+                device = 0;
+            }
         }
         const std::string lib = exe_dir() + "/mpi_openmp_cuda_b200/_lib/libseqalign_cuda.so";
         void* h = dlopen(lib.c_str(), RTLD_NOW | RTLD_LOCAL);

@@ -236,6 +236,12 @@ int sa_plan_pack(const sa_problem* p, int world, void** blob, size_t* blob_bytes
 int sa_plan_pack_into(const sa_problem* p, int world, void* dst, size_t cap, size_t* blob_bytes);
 /* As sa_plan_pack_into with an explicit SA_MODE_*. */
 int sa_plan_pack_mode(const sa_problem* p, int world, int mode, void* dst, size_t cap, size_t* blob_bytes);
+/* The same for sequences [first, first + count) only: row i of that launch's result table is sequence
+ * first + i. sa_session_solve packs a large batch range by range so that packing overlaps the copy and
+ * the kernel of the previous range (the reference prepares all rows, then scores them one by one:
+ * main.c:96-121, 178-183). */
+int sa_plan_pack_range(const sa_problem* p, uint32_t first, uint32_t count, int world, int mode, void* dst, size_t cap,
+                       size_t* blob_bytes);
 void sa_blob_free(void* blob);
 
 /* CPU executor of a packed blob: walks the item list with exactly the tile /
@@ -326,6 +332,11 @@ int sa_session_solve(sa_session* s, const sa_problem* p, int32_t* out3);
 void sa_session_configure(sa_session* s, size_t zero_copy_max_bytes, int direct_out);
 /* Bytes moved over PCIe by the last solve (for benchmark reporting). */
 void sa_session_last_bytes(const sa_session* s, uint64_t* h2d, uint64_t* d2h);
+/* Batches of at least min_seq sequences (default 16384; 0 = never) are packed, copied and launched in
+ * ranges of min_seq/2 or more sequences, so that packing range k+1 on the host overlaps the copy and the
+ * kernel of range k; results are identical. sa_session_last_launches: kernel launches of the last solve. */
+void sa_session_set_pipeline(sa_session* s, size_t min_seq);
+uint32_t sa_session_last_launches(const sa_session* s);
 
 /* ------------------------------------------------------------------- fabric */
 

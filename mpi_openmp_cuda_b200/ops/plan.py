@@ -77,6 +77,20 @@ def blob_size(problem, world: int = 1, mode: str = "auto", split_tiles: bool = F
     return int(need.value)
 
 
+def plan_pack_range(problem, first: int, count: int, world: int = 1, mode: str = "auto") -> PackedBlob:
+    """Plan + pack sequences [first, first + count) only (row i of that launch = sequence first + i): what the
+    native session does range by range for large batches."""
+    lib = N.core()
+    lib.sa_plan_pack_range.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+    need = C.c_size_t()
+    N.check(lib.sa_plan_pack_range(problem.handle, first, count, world, MODES[mode], None, 0, C.byref(need)))
+    buf = np.empty(int(need.value), dtype=np.uint8)
+    got = C.c_size_t()
+    N.check(lib.sa_plan_pack_range(problem.handle, first, count, world, MODES[mode], C.c_void_p(buf.ctypes.data), int(need.value), C.byref(got)))
+    hdr = N.BlobHeader.from_buffer_copy(C.string_at(buf.ctypes.data, C.sizeof(N.BlobHeader)))
+    return PackedBlob(buf, int(got.value), hdr)
+
+
 def plan_pack(problem, world: int = 1, pinned: bool = False, out=None, mode: str = "auto", split_tiles: bool = False) -> PackedBlob:
     """Plan the tiling, partition over `world` GPUs and pack. Raises NativeError with
     code SA_ERR_UNSUPPORTED when the input is outside the GPU executor's limits.

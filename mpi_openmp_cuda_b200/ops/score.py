@@ -95,6 +95,16 @@ class NativeSession:
     def configure(self, zero_copy_max_bytes: int = 0, direct_out: bool = True) -> None:
         self.lib.sa_session_configure(self._h, int(zero_copy_max_bytes), 1 if direct_out else 0)
 
+    def set_pipeline(self, min_seq: int) -> None:
+        """Batches of at least `min_seq` sequences are packed / copied / launched range by range (0 = never)."""
+        self.lib.sa_session_set_pipeline.argtypes = [C.c_void_p, C.c_size_t]
+        self.lib.sa_session_set_pipeline(self._h, int(min_seq))
+
+    def last_launches(self) -> int:
+        self.lib.sa_session_last_launches.restype = C.c_uint32
+        self.lib.sa_session_last_launches.argtypes = [C.c_void_p]
+        return int(self.lib.sa_session_last_launches(self._h))
+
     def last_bytes(self) -> tuple[int, int]:
         a, b = C.c_uint64(), C.c_uint64()
         self.lib.sa_session_last_bytes(self._h, C.byref(a), C.byref(b))

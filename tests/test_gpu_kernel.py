@@ -165,6 +165,30 @@ def test_auto_mode_picks_stream_for_very_large_batches(solver):
     assert np.array_equal(solver.solve(p), ref)
 
 
+def test_large_batches_are_packed_and_launched_range_by_range(solver):
+    """The native session overlaps host packing with copy + kernel for batches of >= 16384 sequences:
+    several launches, same rows as one launch and as the oracle; buffers survive a change of batch size."""
+    p = random_problem(20000, len1=400, len2_range=(1, 90), seed=5)
+    ref = solve_cpu(p, "fast")
+    assert np.array_equal(solver.solve(p), ref)
+    assert solver.session.last_launches() >= 2
+    solver.session.set_pipeline(0)
+    try:
+        assert np.array_equal(solver.solve(p), ref)
+        assert solver.session.last_launches() == 1
+    finally:
+        solver.session.set_pipeline(16384)
+    solver.session.set_pipeline(64)  # force the range path on small batches too, with ranges of uneven size
+    try:
+        for n in (64, 203, 1000, 131):
+            q = random_problem(n, len1=300, len2_range=(1, 320), seed=n)
+            assert np.array_equal(solver.solve(q), solve_cpu(q, "fast"))
+            assert solver.session.last_launches() >= 2
+    finally:
+        solver.session.set_pipeline(16384)
+    assert np.array_equal(solver.solve(p), ref)
+
+
 def test_pair_mode_limits_fall_back_to_tiles(solver):
     from mpi_openmp_cuda_b200.ops._native import NativeError
 

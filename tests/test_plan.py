@@ -282,3 +282,24 @@ def test_empty_sequence_has_no_candidates_in_every_layer(mode):
     blob = plan.plan_pack(p, mode=mode)
     assert blob.seq_table()["ntiles"][0] == 0 and blob.seq_table()["ntiles"][2] == 0
     assert np.array_equal(plan.execute_blob_cpu(blob), naive)
+
+
+@pytest.mark.parametrize("mode", ["tile", "pair", "stream", "auto"])
+def test_packing_a_range_of_sequences_scores_exactly_those_rows(shipped_inputs, mode):
+    """sa_plan_pack_range: what the native session packs range by range for large batches. Row i of a
+    range's launch must be sequence first + i, whatever the range, including ranges with sequences that
+    have no candidates and the empty range."""
+    p = Problem.from_file(shipped_inputs[3][0])
+    want = solve_cpu(p, "fast")
+    for first, count in ((0, p.nseq), (0, 7), (5, 11), (p.nseq - 3, 3), (9, 1), (4, 0)):
+        if count == 0 and mode in ("pair", "stream"):
+            continue  # a forced u16x2 mode needs at least one sequence with candidates
+        blob = plan.plan_pack_range(p, first, count, mode=mode)
+        assert blob.nseq == count
+        got = plan.execute_blob_cpu(blob)
+        assert np.array_equal(got, want[first:first + count])
+    whole = plan.plan_pack(p, mode=mode)
+    ranged = plan.plan_pack_range(p, 0, p.nseq, mode=mode)
+    assert bytes(whole.numpy()[: whole.nbytes]) == bytes(ranged.numpy()[: ranged.nbytes])
+    with pytest.raises(Exception):
+        plan.plan_pack_range(p, p.nseq - 1, 2)
