@@ -141,9 +141,7 @@ void parallel_for(uint32_t n, uint64_t work_bytes, F fn) {
     };
     static const bool no_pool = std::getenv("SA_PACK_POOL") && std::getenv("SA_PACK_POOL")[0] == '0';  // A/B switch
     if (!no_pool && Pool::get()->run(nt, part)) return;
-    std::vector<std::thread> pool;  // the parked workers are busy with another caller's job
-    for (unsigned t = 0; t < nt; ++t) pool.emplace_back([&part, t]() { part(t); });
-    for (auto& th : pool) th.join();
+    fn(0u, n);  // the parked workers are busy with another caller's job (ranges of one batch are packed concurrently)
 }
 
 struct SeqPlan {
@@ -151,10 +149,12 @@ struct SeqPlan {
     int32_t ndiag = 0;
     uint32_t ntiles = 0;
     uint32_t wd_log2 = 0;
+    uint32_t narrow = 0;     // TILE latency mode: a lane owns 8 >> narrow offsets, a warp 256 >> narrow (sa_tile_item.narrow)
     uint32_t crow = kU;
     uint64_t item_cost = 0;  // padded cells per tile
     bool stream = false;     // STREAM mode: one warp walks all rows (no row chunks)
     uint32_t rows_padded() const { return stream ? crow : crow * (kWarps >> wd_log2); }
+    uint32_t tile_offsets() const { return (kWarpDiag >> narrow) << wd_log2; }
 };
 
 SeqPlan plan_sequence(uint32_t len1, uint32_t len2) {
@@ -412,7 +412,13 @@ int sa_plan_pack_range(const sa_problem* p, uint32_t first, uint32_t count, int 
         // the longest item's rows over more warps (narrower offset tiles, more of them) until the SMs
         // are used up. The reference scores a whole row in ONE block (cudaFunctions.cu:210-216).
         const uint64_t slots = (uint64_t)SA_PLAN_SMS * (uint64_t)world;
-        auto steps = [](const SeqPlan& sp) { return (uint64_t)sp.crow + 2ull * (kWarps >> sp.wd_log2); };
+        // an item's duration in ninths of a row-step: a row costs (R + 1) table lookups per lane, the merge
+        // about two row-steps per row chunk
+        auto steps = [](const SeqPlan& sp) { return (uint64_t)sp.crow * ((kR >> sp.narrow) + 1u) + 18ull * (kWarps >> sp.wd_log2); };
+        static const uint32_t max_narrow = [] {
+            const char* e = std::getenv("SA_PLAN_MAX_NARROW");  // experiments: 0 switches narrow tiles off
+            return e ? (uint32_t)std::min(SA_MAX_NARROW, std::max(0, std::atoi(e))) : (uint32_t)SA_MAX_NARROW;
+        }();
         uint64_t nit = 0;
         for (uint32_t s = 0; s < nseq; ++s) nit += plans[s].ntiles;
         if (nit < slots) {
@@ -426,10 +432,13 @@ int sa_plan_pack_range(const sa_problem* p, uint32_t first, uint32_t count, int 
                 std::pop_heap(heap.begin(), heap.end());
                 const uint32_t worst = heap.back().second;
                 heap.pop_back();
-                if (plans[worst].wd_log2 == 0) break;  // the longest item cannot be split further
                 SeqPlan sp = plans[worst];
-                sp.wd_log2 -= 1;
-                const uint32_t wr = kWarps >> sp.wd_log2, tn = kWarpDiag << sp.wd_log2;
+                // first more row chunks over narrower tiles; when all 16 warps already are row chunks, fewer
+                // offsets per lane (a 16-warp CTA then covers 128 or 64 offsets instead of 256)
+                if (sp.wd_log2 > 0) sp.wd_log2 -= 1;
+                else if (sp.narrow < max_narrow) sp.narrow += 1;
+                else break;  // the longest item cannot be split further
+                const uint32_t wr = kWarps >> sp.wd_log2, tn = sp.tile_offsets();
                 const uint32_t d = sp.ndiag == 0 ? 1u : (uint32_t)sp.ndiag;
                 sp.crow = round_up((sp.len + wr - 1) / wr, kU);
                 sp.ntiles = (d + tn - 1) / tn;
@@ -461,7 +470,7 @@ int sa_plan_pack_range(const sa_problem* p, uint32_t first, uint32_t count, int 
         for (uint32_t s = 0; s < nseq; ++s) {
             max_rows = std::max(max_rows, plans[s].rows_padded());
             if (plans[s].ntiles)
-                max_window = std::max(max_window, round_up(plans[s].rows_padded() + (kWarpDiag << plans[s].wd_log2), 16));
+                max_window = std::max(max_window, round_up(plans[s].rows_padded() + plans[s].tile_offsets(), 16));
             padded_cells += plans[s].item_cost * plans[s].ntiles;
             nitems64 += plans[s].ntiles;
         }
@@ -739,6 +748,7 @@ int sa_plan_pack_range(const sa_problem* p, uint32_t first, uint32_t count, int 
             fat[i].crow = d.crow;
             fat[i].ntiles = d.ntiles;
             fat[i].wd_log2 = d.wd_log2;
+            fat[i].narrow = (uint8_t)plans[items[i].seq].narrow;
             fat[i].home = d.home;
         }
     }
@@ -973,7 +983,12 @@ int sa_blob_score_items_cpu(const void* blob, size_t blob_bytes, uint32_t first_
         sd.ntiles = fat[it].ntiles, sd.wd_log2 = fat[it].wd_log2, sd.home = fat[it].home;
         const unsigned char* s2 = b.base + sd.off;
         const uint32_t wd = 1u << sd.wd_log2, wr = kWarps / wd, crow = sd.crow;
-        const uint32_t tn = kWarpDiag * wd, n0 = tile * tn;
+        if (fat[it].narrow > SA_MAX_NARROW) {
+            set_error("sa_blob_score_items_cpu: bad tile geometry");
+            return SA_ERR_ARG;
+        }
+        const uint32_t R = kR >> fat[it].narrow, warp_diag = 32u * R;  // offsets per lane / per warp of this item
+        const uint32_t tn = warp_diag * wd, n0 = tile * tn;
         if ((uint64_t)n0 + wr * crow + tn > b.h->len1_padded) {
             set_error("sa_blob_score_items_cpu: window outside padded Seq1");
             return SA_ERR_ARG;
@@ -981,22 +996,22 @@ int sa_blob_score_items_cpu(const void* blob, size_t blob_bytes, uint32_t first_
         for (uint32_t w = 0; w < kWarps; ++w) {
             const uint32_t g = w & (wd - 1), q = w >> sd.wd_log2;
             for (uint32_t lane = 0; lane < 32; ++lane) {
-                const uint32_t d0 = g * kWarpDiag + lane * kR;
+                const uint32_t d0 = g * warp_diag + lane * R;
                 int32_t P[kR + 1], best[kR];
-                for (uint32_t r = 0; r <= kR; ++r) P[r] = 0;
-                for (uint32_t r = 0; r < kR; ++r) best[r] = kNeg;
+                for (uint32_t r = 0; r <= R; ++r) P[r] = 0;
+                for (uint32_t r = 0; r < R; ++r) best[r] = kNeg;
                 for (uint32_t i = q * crow; i < (q + 1) * crow; ++i) {
                     const unsigned code2 = s2[i];
-                    for (uint32_t r = 0; r <= kR; ++r) P[r] += b.value(code2, b.seq1[n0 + i + d0 + r]);
-                    for (uint32_t r = 0; r < kR; ++r) best[r] = std::max(best[r], P[r] - P[r + 1]);
+                    for (uint32_t r = 0; r <= R; ++r) P[r] += b.value(code2, b.seq1[n0 + i + d0 + r]);
+                    for (uint32_t r = 0; r < R; ++r) best[r] = std::max(best[r], P[r] - P[r + 1]);
                 }
-                for (uint32_t r = 0; r <= kR; ++r) csum[((size_t)w * (kR + 1) + r) * 32 + lane] = P[r];
-                for (uint32_t r = 0; r < kR; ++r) cmax[((size_t)w * kR + r) * 32 + lane] = best[r];
+                for (uint32_t r = 0; r <= R; ++r) csum[((size_t)w * (kR + 1) + r) * 32 + lane] = P[r];
+                for (uint32_t r = 0; r < R; ++r) cmax[((size_t)w * kR + r) * 32 + lane] = best[r];
             }
         }
         uint64_t tile_key = 0;
         for (uint32_t d = 0; d < tn; ++d) {
-            const uint32_t g = d / kWarpDiag, lane = (d % kWarpDiag) / kR, r = d % kR;
+            const uint32_t g = d / warp_diag, lane = (d % warp_diag) / R, r = d % R;
             int32_t A = 0, T0 = 0, T1 = 0, M = kNeg;
             for (uint32_t q = 0; q < wr; ++q) {
                 const uint32_t w = q * wd + g;

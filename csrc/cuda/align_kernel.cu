@@ -28,6 +28,8 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <thread>
+#include <vector>
 
 #include "ptx_helpers.cuh"
 #include "seqalign.h"
@@ -437,6 +439,59 @@ __device__ __forceinline__ void launch_epilogue(const KParams& p) {
 // kFabric = false: one GPU owns everything (p.key/p.cnt/p.out/p.ctrl are local).
 // kFabric = true : one of `world` cooperating launches, one per GPU (see sa_cuda_fabric_solve and the
 //   data-movement notes above fabric_prologue); the caller has run fabric_prologue, so s_hdr is valid.
+// TILE scan of one warp: R consecutive offsets per lane (8, or 4 for the narrow tiles of latency mode), rows
+// [0, crow) of the warp's row chunk. Difference form (see scan8_u16x2): D[r] = P[r] - P[r+1] is carried, the
+// running maximum takes two rows per VIMNMX3. Writes the warp's R+1 prefixes and R maxima for the merge.
+template <int R>
+__device__ __forceinline__ void tile_scan(const unsigned char* lut_b, const unsigned char* wp, const unsigned char* sp, uint32_t crow,
+                                          int* csum, int* cmax, uint32_t warp, uint32_t lane) {
+    int D[R], best[R], PR = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) D[r] = 0, best[r] = kNeg;
+    // letters of columns (row + d0 + k): wp is 8-byte aligned for R = 8, 4-byte aligned for R = 4
+    auto load8 = [](const unsigned char* a) -> uint2 {
+        if (R == kR) return *reinterpret_cast<const uint2*>(a);
+        return make_uint2(*reinterpret_cast<const uint32_t*>(a), *reinterpret_cast<const uint32_t*>(a + 4));
+    };
+    uint2 lw0 = load8(wp);
+    for (uint32_t row = 0; row < crow; row += kU) {
+        const uint2 lw1 = load8(wp + row + kU);
+        const uint2 sc = *reinterpret_cast<const uint2*>(sp + row);
+        uint32_t L[2 * kU];
+#pragma unroll
+        for (int k = 0; k < kU; ++k) {
+            L[k] = byte_of(lw0.x, lw0.y, k);
+            L[kU + k] = byte_of(lw1.x, lw1.y, k);
+        }
+#pragma unroll
+        for (int u = 0; u < kU; u += 2) {
+            const unsigned char* lrow0 = lut_b + byte_of(sc.x, sc.y, u) * (SA_ALPHABET * 4u);
+            const unsigned char* lrow1 = lut_b + byte_of(sc.x, sc.y, u + 1) * (SA_ALPHABET * 4u);
+            int v[R + 1], w[R + 1];
+#pragma unroll
+            for (int r = 0; r <= R; ++r) v[r] = *reinterpret_cast<const int*>(lrow0 + L[u + r]);
+#pragma unroll
+            for (int r = 0; r <= R; ++r) w[r] = *reinterpret_cast<const int*>(lrow1 + L[u + 1 + r]);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const int d0 = D[r] + v[r] - v[r + 1];
+                D[r] = d0 + w[r] - w[r + 1];
+                best[r] = __vimax3_s32(best[r], d0, D[r]);
+            }
+            PR += v[R] + w[R];
+        }
+        lw0 = lw1;
+    }
+    int P[R + 1];
+    P[R] = PR;
+#pragma unroll
+    for (int r = R - 1; r >= 0; --r) P[r] = P[r + 1] + D[r];
+#pragma unroll
+    for (int r = 0; r <= R; ++r) csum[(warp * (kR + 1) + r) * 32 + lane] = P[r];
+#pragma unroll
+    for (int r = 0; r < R; ++r) cmax[(warp * kR + r) * 32 + lane] = best[r];
+}
+
 template <bool kFabric>
 __device__ __forceinline__ void score_body(const KParams& p, const bool epilogue_later = false) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -540,7 +595,8 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool epilogue
         const uint32_t seq = sd.seq, tile = sd.tile;
         const uint32_t wd_log2 = sd.wd_log2, wd = 1u << wd_log2, wr = (uint32_t)kWarps >> wd_log2;
         const uint32_t crow = sd.crow, rows_padded = crow * wr;
-        const uint32_t tn = (uint32_t)SA_DIAG_PER_WARP << wd_log2, n0 = tile * tn;
+        const uint32_t rl = 3u - sd.narrow;  // log2(offsets per lane)
+        const uint32_t tn = (32u << rl) << wd_log2, n0 = tile * tn;
 
         unsigned long long* const keyp =
             (kFabric ? reinterpret_cast<unsigned long long*>(p.peer[sd.home] + p.off_key) : p.key) + seq;
@@ -563,49 +619,10 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool epilogue
         // ---- scan: this warp = offset group g, row chunk q
         {
             const uint32_t g = warp & (wd - 1u), q = warp >> wd_log2;
-            const uint32_t d0 = g * SA_DIAG_PER_WARP + lane * kR;
-            const unsigned char* wp = win + d0 + q * crow;  // letters of column (row + d0 + k)
-            const unsigned char* sp = s2 + q * crow;
-            int D[kR], best[kR], P8 = 0;  // difference form, see scan8_u16x2
-#pragma unroll
-            for (int r = 0; r < kR; ++r) D[r] = 0, best[r] = kNeg;
-            uint2 lw0 = *reinterpret_cast<const uint2*>(wp);
-            for (uint32_t row = 0; row < crow; row += kU) {
-                const uint2 lw1 = *reinterpret_cast<const uint2*>(wp + row + kU);
-                const uint2 sc = *reinterpret_cast<const uint2*>(sp + row);
-                uint32_t L[2 * kU];
-#pragma unroll
-                for (int k = 0; k < kU; ++k) {
-                    L[k] = byte_of(lw0.x, lw0.y, k);
-                    L[kU + k] = byte_of(lw1.x, lw1.y, k);
-                }
-#pragma unroll
-                for (int u = 0; u < kU; u += 2) {
-                    const unsigned char* lrow0 = lut_b + byte_of(sc.x, sc.y, u) * (SA_ALPHABET * 4u);
-                    const unsigned char* lrow1 = lut_b + byte_of(sc.x, sc.y, u + 1) * (SA_ALPHABET * 4u);
-                    int v[kR + 1], w[kR + 1];
-#pragma unroll
-                    for (int r = 0; r <= kR; ++r) v[r] = *reinterpret_cast<const int*>(lrow0 + L[u + r]);
-#pragma unroll
-                    for (int r = 0; r <= kR; ++r) w[r] = *reinterpret_cast<const int*>(lrow1 + L[u + 1 + r]);
-#pragma unroll
-                    for (int r = 0; r < kR; ++r) {
-                        const int d0 = D[r] + v[r] - v[r + 1];
-                        D[r] = d0 + w[r] - w[r + 1];
-                        best[r] = __vimax3_s32(best[r], d0, D[r]);
-                    }
-                    P8 += v[kR] + w[kR];
-                }
-                lw0 = lw1;
-            }
-            int P[kR + 1];
-            P[kR] = P8;
-#pragma unroll
-            for (int r = kR - 1; r >= 0; --r) P[r] = P[r + 1] + D[r];
-#pragma unroll
-            for (int r = 0; r <= kR; ++r) csum[(warp * (kR + 1) + r) * 32 + lane] = P[r];
-#pragma unroll
-            for (int r = 0; r < kR; ++r) cmax[(warp * kR + r) * 32 + lane] = best[r];
+            if (sd.narrow == 0)
+                tile_scan<kR>(lut_b, win + (g * 32u + lane) * kR + q * crow, s2 + q * crow, crow, csum, cmax, warp, lane);
+            else
+                tile_scan<kR / 2>(lut_b, win + (g * 32u + lane) * (kR / 2) + q * crow, s2 + q * crow, crow, csum, cmax, warp, lane);
         }
         __syncthreads();
         if (tl_any && was_first && tid == 0) atomicMax(&times[13], global_ns());
@@ -613,7 +630,7 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool epilogue
         // ---- merge row chunks in order, score every offset of the tile, keep the best
         unsigned long long mykey = 0ull;
         for (uint32_t t = tid; t < tn; t += kThreads) {
-            const uint32_t l = t & 31u, r = (t >> 5) & 7u, g = t >> 8;
+            const uint32_t l = t & 31u, r = (t >> 5) & ((1u << rl) - 1u), g = t >> (5u + rl);
             int A = 0, T0 = 0, T1 = 0, M = kNeg;
             for (uint32_t q = 0; q < wr; ++q) {
                 const uint32_t w = (q << wd_log2) + g;
@@ -625,7 +642,7 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool epilogue
                 T0 += s0;
                 T1 += s1;
             }
-            const uint32_t n = n0 + g * SA_DIAG_PER_WARP + l * kR + r;
+            const uint32_t n = n0 + (((g << 5) + l) << rl) + r;
             if (sd.ndiag == 0) {
                 if (n == 0) mykey = pack_key(T0, 0u);  // equal lengths: one candidate (cudaFunctions.cu:74-106)
             } else if (n < (uint32_t)sd.ndiag) {
@@ -1508,7 +1525,6 @@ struct sa_session {
     bool direct_out = true;            // result rows are written straight into pinned memory
     size_t pipe_min_seq = 16384;       // batches at least this large are packed and launched in ranges of >= half of it
                                        // (8192 sequences keep a range above AUTO's threshold for the STREAM kernel)
-    cudaEvent_t half_free[2] = {nullptr, nullptr};  // pipelined path: the H2D copy out of each half of h_in has finished
     uint32_t last_launches = 0;
 };
 
@@ -1540,8 +1556,6 @@ void sa_session_destroy(sa_session* s) {
     cudaFree(s->d_blob);
     cudaFree(s->d_out);
     cudaFree(s->d_scratch);
-    for (cudaEvent_t e : s->half_free)
-        if (e) cudaEventDestroy(e);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
 }
@@ -1594,13 +1608,14 @@ int session_reserve(sa_session* s, size_t blob_bytes, size_t nseq) {
 }
 
 // Large batches: the host needs longer to pack the problem than the GPU needs to score it (input3 x 1024:
-// 4.3 ms against 1.3 ms on a B200 box), so the batch is cut into ranges of sequences and range k+1 is planned
-// and packed while range k is copied and scored. Two halves of the pinned and of the device buffer
-// alternate; everything runs in order on the session's stream, so the self-cleaning scratch is shared.
+// 4.3 ms against 1.3 ms on a B200 box, and most of the 4.3 is single-threaded planning), so the batch is cut
+// into ranges of sequences. A few host threads plan and pack one range each, concurrently, every range into
+// its own slot of the pinned and of the device buffer; whoever finishes a range issues its copy and its
+// launch on the session's stream (in whatever order: rows are disjoint, the self-cleaning scratch is
+// shared by launches that run one after the other). Packing overlaps packing, copies and kernels.
 int session_solve_pipelined(sa_session* s, const sa_problem* prob, int32_t* out3, size_t nseq) {
     const size_t nranges = std::min<size_t>(8, std::max<size_t>(2, nseq / std::max<size_t>(1, s->pipe_min_seq / 2)));
-    for (cudaEvent_t& e : s->half_free)
-        if (!e) SA_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    const unsigned nthreads = (unsigned)std::min<size_t>(nranges, std::max(1u, std::min(4u, std::thread::hardware_concurrency() / 2)));
     int rc = session_reserve(s, s->h_in_cap, nseq);  // result table and scratch for the whole batch
     if (rc != SA_OK) return rc;
     auto rezero = [&]() {
@@ -1608,75 +1623,97 @@ int session_solve_pipelined(sa_session* s, const sa_problem* prob, int32_t* out3
         cudaMemsetAsync(s->d_scratch, 0, sa_cuda_scratch_bytes((uint32_t)s->d_scratch_cap), s->stream);
     };
     int32_t* const out_dev = reinterpret_cast<int32_t*>(s->direct_out ? s->h_out : s->d_out);
-    uint64_t h2d = 0;
-    bool half_used[2] = {false, false};
-    s->last_launches = 0;
-    for (size_t k = 0; k < nranges; ++k) {
-        const uint32_t first = (uint32_t)(nseq * k / nranges), count = (uint32_t)(nseq * (k + 1) / nranges) - first;
-        const int half = (int)(k & 1);
-        size_t got = 0;
-        for (int attempt = 0;; ++attempt) {
-            const size_t half_cap = s->h_in_cap / 2 & ~(size_t)255;
-            if (half_used[half]) {
-                const cudaError_t e = cudaEventSynchronize(s->half_free[half]);  // its previous copy has left the pinned half
-                if (e != cudaSuccess) return fail(e, "cudaEventSynchronize");
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        const size_t slot = (std::min(s->h_in_cap, s->d_blob_cap) / nranges) & ~(size_t)255;
+        std::atomic<size_t> next{0};
+        std::atomic<size_t> need_max{0};  // a range that did not fit its slot: the largest size asked for
+        std::atomic<int> failed{SA_OK};
+        std::mutex launch_mutex, err_mutex;
+        std::string err_text;
+        uint64_t h2d = 0;
+        uint32_t launches = 0;
+        auto worker = [&]() {
+            if (cudaSetDevice(s->device) != cudaSuccess) {
+                failed.store(SA_ERR_CUDA);
+                return;
             }
-            rc = half_cap ? sa_plan_pack_range(prob, first, count, 1, SA_MODE_AUTO, s->h_in + half * half_cap, half_cap, &got) : SA_ERR_SMALL_BUFFER;
-            if (rc == SA_ERR_SMALL_BUFFER && attempt == 0) {
-                if (!half_cap) {
-                    rc = sa_plan_pack_range(prob, first, count, 1, SA_MODE_AUTO, nullptr, 0, &got);
-                    if (rc != SA_OK) return rc;
+            for (;;) {
+                const size_t k = next.fetch_add(1);
+                if (k >= nranges || failed.load() != SA_OK) return;
+                const uint32_t first = (uint32_t)(nseq * k / nranges), count = (uint32_t)(nseq * (k + 1) / nranges) - first;
+                unsigned char* const h_blob = s->h_in + k * slot;
+                size_t got = 0;
+                int r = sa_plan_pack_range(prob, first, count, 1, SA_MODE_AUTO, slot ? h_blob : nullptr, slot, &got);
+                if (r == SA_OK && !slot) r = SA_ERR_SMALL_BUFFER;
+                if (r == SA_ERR_SMALL_BUFFER) {
+                    size_t cur = need_max.load();
+                    while (got > cur && !need_max.compare_exchange_weak(cur, got)) {
+                    }
+                    continue;  // keep sizing the other ranges; nothing more is launched in this attempt
                 }
-                // growing the buffers frees them: nothing may be in flight
-                const cudaError_t e = cudaStreamSynchronize(s->stream);
-                if (e != cudaSuccess) return fail(e, "cudaStreamSynchronize");
-                half_used[0] = half_used[1] = false;
-                rc = session_reserve(s, 2 * (got + got / 4 + 256), nseq);
-                if (rc != SA_OK) return rc;
-                continue;
+                if (r == SA_OK && need_max.load() != 0) continue;
+                if (r == SA_OK) {
+                    std::lock_guard<std::mutex> g(launch_mutex);
+                    unsigned char* const d_blob = s->d_blob + k * slot;
+                    const cudaError_t e = cudaMemcpyAsync(d_blob, h_blob, got, cudaMemcpyHostToDevice, s->stream);
+                    if (e != cudaSuccess) {
+                        r = fail(e, "cudaMemcpyAsync(range)");
+                    } else {
+                        h2d += got;
+                        const sa_blob_header* h = reinterpret_cast<const sa_blob_header*>(h_blob);  // read at launch time only
+                        if (h->nseq) {
+                            r = sa_cuda_solve_blob(d_blob, h, out_dev + 4 * (size_t)first, s->d_scratch, s->stream);
+                            if (r == SA_OK) ++launches;
+                        }
+                    }
+                }
+                if (r != SA_OK) {
+                    std::lock_guard<std::mutex> g(err_mutex);
+                    if (failed.load() == SA_OK) {
+                        err_text = sa_last_error();  // the message lives in this thread: hand it to the caller's
+                        failed.store(r);
+                    }
+                    return;
+                }
             }
-            break;
-        }
-        if (rc != SA_OK) {
+        };
+        std::vector<std::thread> pool;
+        for (unsigned t = 1; t < nthreads; ++t) pool.emplace_back(worker);
+        worker();
+        for (auto& th : pool) th.join();
+        if (failed.load() != SA_OK) {
             rezero();
-            return rc;  // SA_ERR_UNSUPPORTED: the caller falls back to the CPU for the whole batch
+            sa_set_last_error(err_text.c_str());
+            return failed.load();  // SA_ERR_UNSUPPORTED: the caller falls back to the CPU for the whole batch
         }
-        const size_t half_cap = s->h_in_cap / 2 & ~(size_t)255, dev_half = s->d_blob_cap / 2 & ~(size_t)255;
-        const unsigned char* h_blob = s->h_in + half * half_cap;
-        unsigned char* d_blob = s->d_blob + half * dev_half;
-        cudaError_t e = cudaMemcpyAsync(d_blob, h_blob, got, cudaMemcpyHostToDevice, s->stream);
-        if (e == cudaSuccess) e = cudaEventRecord(s->half_free[half], s->stream);
+        if (need_max.load() != 0) {
+            // first large batch of this session (or a larger one than before): grow the buffers — which frees
+            // them, so nothing may be in flight — and start over
+            const cudaError_t e = cudaStreamSynchronize(s->stream);
+            if (e != cudaSuccess) return fail(e, "cudaStreamSynchronize");
+            rc = session_reserve(s, nranges * ((need_max.load() + need_max.load() / 8 + 511) & ~(size_t)255), nseq);
+            if (rc != SA_OK) return rc;
+            continue;
+        }
+        cudaError_t e = cudaSuccess;
+        if (!s->direct_out) e = cudaMemcpyAsync(s->h_out, s->d_out, nseq * sizeof(int4), cudaMemcpyDeviceToHost, s->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
         if (e != cudaSuccess) {
             rezero();
-            return fail(e, "cudaMemcpyAsync(range)");
+            return fail(e, "cudaStreamSynchronize");
         }
-        half_used[half] = true;
-        h2d += got;
-        const sa_blob_header* h = reinterpret_cast<const sa_blob_header*>(h_blob);  // read at launch time only
-        if (h->nseq) {
-            rc = sa_cuda_solve_blob(d_blob, h, out_dev + 4 * (size_t)first, s->d_scratch, s->stream);
-            if (rc != SA_OK) {
-                rezero();
-                return rc;
-            }
-            ++s->last_launches;
+        s->h2d_bytes = h2d;
+        s->d2h_bytes = nseq * sizeof(int4);
+        s->last_launches = launches;
+        for (size_t i = 0; i < nseq; ++i) {
+            out3[3 * i] = s->h_out[i].x;
+            out3[3 * i + 1] = s->h_out[i].y;
+            out3[3 * i + 2] = s->h_out[i].z;
         }
+        return SA_OK;
     }
-    cudaError_t e = cudaSuccess;
-    if (!s->direct_out) e = cudaMemcpyAsync(s->h_out, s->d_out, nseq * sizeof(int4), cudaMemcpyDeviceToHost, s->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
-    if (e != cudaSuccess) {
-        rezero();
-        return fail(e, "cudaStreamSynchronize");
-    }
-    s->h2d_bytes = h2d;
-    s->d2h_bytes = nseq * sizeof(int4);
-    for (size_t i = 0; i < nseq; ++i) {
-        out3[3 * i] = s->h_out[i].x;
-        out3[3 * i + 1] = s->h_out[i].y;
-        out3[3 * i + 2] = s->h_out[i].z;
-    }
-    return SA_OK;
+    sa_set_last_error("sa_session_solve: a range did not fit the buffers sized for it");
+    return SA_ERR_NOMEM;
 }
 }  // namespace
 

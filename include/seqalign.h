@@ -205,8 +205,13 @@ typedef struct sa_tile_item {
     int32_t ndiag;    /* = seqtab[seq].ndiag */
     uint16_t len, crow, ntiles;
     uint8_t wd_log2, home;
-    uint32_t pad[2];
+    uint8_t narrow;   /* a lane owns SA_DIAG_PER_LANE >> narrow offsets: tile = (256 >> narrow) << wd_log2 offsets.
+                         Non-zero only when the whole problem is fewer items than SMs (latency mode): the longest
+                         items are cut into narrower tiles so that more SMs share them. */
+    uint8_t pad8[3];
+    uint32_t pad;
 } sa_tile_item; /* 32 bytes */
+#define SA_MAX_NARROW 1
 
 /* STREAM mode: one self-contained record per pair of sequences scored as u16x2 lanes (what
  * sa_tile_item is for TILE mode): a warp needs the item and this record, nothing else. */

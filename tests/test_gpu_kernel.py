@@ -253,3 +253,20 @@ def test_degenerate_problems(solver):
     none_fit = Problem.from_parts((1, 2, 3, 4), "AB", ["ABC", "ABCD"])  # every sequence longer than Seq1
     assert solver.solve(none_fit).tolist() == [[-2147483648, 0, 0]] * 2
     assert solver.solve_packed(solver.pack(none_fit)).tolist() == [[-2147483648, 0, 0]] * 2
+
+
+@pytest.mark.parametrize("mode", ["tile", "pair", "stream"])
+def test_every_kernel_against_the_literal_restatement(solver, shipped_inputs, mode):
+    """The fast oracle shares the kernels' prefix-difference algebra; the naive one re-scores every (n, k)
+    candidate letter by letter as the reference kernel means to (cudaFunctions.cu:116-168). Small inputs, since
+    it is O(len1 * len2^2): the shipped ones that are small, ties, and random problems with every weight sign."""
+    problems = [Problem.from_file(shipped_inputs[i][0]) for i in (1, 2, 5, 6)]
+    problems.append(Problem.from_parts((3, 1, 2, 5), "ACDEFGHIKL" * 12, ["ACDEFGHIKL" * 3, "GHIKLACDEF" * 2, "L", "AC"]))
+    for seed in range(4):
+        problems.append(random_problem(24, len1=150, len2_range=(1, 150), seed=100 + seed))
+    problems.append(random_problem(12, len1=90, len2_range=(1, 60), seed=7, weights=(0, 5, 0, 1)))
+    for p in problems:
+        want = solve_cpu(p, "naive")
+        blob = solver.pack(p, mode=mode)
+        assert blob.mode == mode
+        assert np.array_equal(solver.solve_packed(blob), want)
