@@ -17,7 +17,7 @@ CUDA_SRC := csrc/cuda/align_kernel.cu csrc/cuda/fabric_bench.cu csrc/cuda/native
 CORE_LIB := $(LIBDIR)/libseqalign_core.so
 CUDA_LIB := $(LIBDIR)/libseqalign_cuda.so
 
-.PHONY: build core cuda clean run runOn2 test sass asan tsan microbench tc_scan startup_probe
+.PHONY: build core cuda clean run runOn2 test sass asan tsan microbench tc_scan startup_probe cluster_probe
 
 build: core cuda final
 
@@ -48,6 +48,12 @@ tc_scan: build/tc_scan
 build/tc_scan: csrc/cuda/tc_scan.cu csrc/cuda/ptx_helpers.cuh
 	@mkdir -p build
 	$(NVCC) -O3 -std=c++17 $(GENCODE) -lineinfo -Xptxas -v -o $@ $<
+
+# Cluster launch + multicast bulk copy for the TILE start-up, measured: profiles/cluster_probe.json
+cluster_probe: build/cluster_probe
+build/cluster_probe: csrc/cuda/cluster_probe.cu csrc/cuda/ptx_helpers.cuh
+	@mkdir -p build
+	$(NVCC) -O3 -std=c++17 $(GENCODE) -lineinfo -o $@ $<
 
 # Cold-start breakdown of a CUDA process (driver init / context / module load): profiles/cold_start.txt
 startup_probe: build/startup_probe

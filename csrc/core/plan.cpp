@@ -54,7 +54,9 @@ inline uint32_t round_up(uint32_t v, uint32_t m) { return (v + m - 1) / m * m; }
 // Host threads for the packer's bulk loops (the reference's only OpenMP use is also input preparation,
 // main.c:82,96 — there it races on stdin). The workers are started once and parked on a condition
 // variable: a large batch is packed range by range (sa_plan_pack_range), and starting 15 threads per range
-// would cost more than the range's share of the work.
+// would cost more than the range's share of the work. Several callers may have a job open at once (the
+// ranges of one batch are packed concurrently): a job is a counter of chunks, workers take chunks from
+// whichever job has some left, and every caller works on its own job too.
 class Pool {
    public:
     static Pool* get() {
@@ -73,75 +75,86 @@ class Pool {
         return p;
     }
     unsigned size() const { return nworkers_ + 1; }
-    // fn(t) for t in [0, nt), t = 0 on the calling thread; false when another caller holds the pool
+    // fn(c) for every chunk c in [0, nchunks); returns when all of them have run
     template <typename F>
-    bool run(unsigned nt, F&& fn) {
-        std::unique_lock<std::mutex> busy(busy_, std::try_to_lock);
-        if (!busy.owns_lock()) return false;
+    void run(unsigned nchunks, F&& fn) {
+        Job job;
+        job.fn = [&fn](unsigned c) { fn(c); };
+        job.n = nchunks;
+        job.left = nchunks;
         {
             std::lock_guard<std::mutex> g(m_);
-            job_ = [&fn](unsigned t) { fn(t); };
-            want_ = nt - 1;
-            pending_ = nt - 1;
-            ++gen_;
+            jobs_.push_back(&job);
         }
         wake_.notify_all();
-        fn(0u);
+        for (;;) {  // the caller takes chunks of its own job
+            const unsigned c = job.next.fetch_add(1, std::memory_order_relaxed);
+            if (c >= nchunks) break;
+            fn(c);
+            job.left.fetch_sub(1, std::memory_order_acq_rel);
+        }
         std::unique_lock<std::mutex> g(m_);
-        done_.wait(g, [&] { return pending_ == 0; });
-        job_ = nullptr;
-        return true;
+        jobs_.erase(std::find(jobs_.begin(), jobs_.end(), &job));  // no new worker can pick it up any more
+        done_.wait(g, [&] { return job.left.load(std::memory_order_acquire) == 0 && job.users == 0; });
     }
 
    private:
+    struct Job {
+        std::function<void(unsigned)> fn;
+        unsigned n = 0;
+        std::atomic<unsigned> next{0}, left{0};
+        unsigned users = 0;  // workers currently inside this job (guarded by m_)
+    };
     static std::atomic<Pool*>& instance() {
         static std::atomic<Pool*> p{nullptr};
         return p;
     }
     explicit Pool(unsigned n) : nworkers_(n > 1 ? n - 1 : 0) {
-        for (unsigned i = 0; i < nworkers_; ++i) std::thread([this, i] { loop(i + 1); }).detach();
+        for (unsigned i = 0; i < nworkers_; ++i) std::thread([this] { loop(); }).detach();
     }
-    void loop(unsigned id) {
-        unsigned seen = 0;
+    Job* pick() {  // m_ held
+        for (Job* j : jobs_)
+            if (j->next.load(std::memory_order_relaxed) < j->n) return j;
+        return nullptr;
+    }
+    void loop() {
+        std::unique_lock<std::mutex> g(m_);
         for (;;) {
-            std::function<void(unsigned)> job;
-            {
-                std::unique_lock<std::mutex> g(m_);
-                wake_.wait(g, [&] { return gen_ != seen; });
-                seen = gen_;
-                if (id > want_) continue;  // this job uses fewer threads
-                job = job_;
+            Job* j = nullptr;
+            wake_.wait(g, [&] { return (j = pick()) != nullptr; });
+            ++j->users;
+            g.unlock();
+            for (;;) {
+                const unsigned c = j->next.fetch_add(1, std::memory_order_relaxed);
+                if (c >= j->n) break;
+                j->fn(c);
+                j->left.fetch_sub(1, std::memory_order_acq_rel);
             }
-            job(id);
-            {
-                std::lock_guard<std::mutex> g(m_);
-                if (--pending_ == 0) done_.notify_one();
-            }
+            g.lock();
+            --j->users;
+            done_.notify_all();
         }
     }
     const unsigned nworkers_;
-    std::mutex m_, busy_;
+    std::mutex m_;
     std::condition_variable wake_, done_;
-    std::function<void(unsigned)> job_;
-    unsigned gen_ = 0, want_ = 0, pending_ = 0;
+    std::vector<Job*> jobs_;
 };
 
-// Static split of [0, n) over host threads when the job is big enough to pay for them.
+// Split of [0, n) over host threads when the job is big enough to pay for them.
 template <typename F>
 void parallel_for(uint32_t n, uint64_t work_bytes, F fn) {
-    unsigned nt = work_bytes < (1u << 20) ? 1u : Pool::get()->size();
-    if (nt > n) nt = n ? n : 1u;
-    if (nt <= 1) {
+    static const bool no_pool = std::getenv("SA_PACK_POOL") && std::getenv("SA_PACK_POOL")[0] == '0';  // A/B switch
+    unsigned nc = (work_bytes < (1u << 20) || no_pool) ? 1u : 2u * Pool::get()->size();
+    if (nc > n) nc = n ? n : 1u;
+    if (nc <= 1) {
         fn(0u, n);
         return;
     }
-    auto part = [&](unsigned t) {
-        const uint32_t a = (uint32_t)((uint64_t)n * t / nt), b = (uint32_t)((uint64_t)n * (t + 1) / nt);
+    Pool::get()->run(nc, [&](unsigned c) {
+        const uint32_t a = (uint32_t)((uint64_t)n * c / nc), b = (uint32_t)((uint64_t)n * (c + 1) / nc);
         fn(a, b);
-    };
-    static const bool no_pool = std::getenv("SA_PACK_POOL") && std::getenv("SA_PACK_POOL")[0] == '0';  // A/B switch
-    if (!no_pool && Pool::get()->run(nt, part)) return;
-    fn(0u, n);  // the parked workers are busy with another caller's job (ranges of one batch are packed concurrently)
+    });
 }
 
 struct SeqPlan {

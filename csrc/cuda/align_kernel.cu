@@ -439,7 +439,7 @@ __device__ __forceinline__ void launch_epilogue(const KParams& p) {
 // kFabric = false: one GPU owns everything (p.key/p.cnt/p.out/p.ctrl are local).
 // kFabric = true : one of `world` cooperating launches, one per GPU (see sa_cuda_fabric_solve and the
 //   data-movement notes above fabric_prologue); the caller has run fabric_prologue, so s_hdr is valid.
-// TILE scan of one warp: R consecutive offsets per lane (8, or 4 for the narrow tiles of latency mode), rows
+// TILE scan of one warp: R consecutive offsets per lane (8, or 4 / 2 for the narrow tiles of latency mode), rows
 // [0, crow) of the warp's row chunk. Difference form (see scan8_u16x2): D[r] = P[r] - P[r+1] is carried, the
 // running maximum takes two rows per VIMNMX3. Writes the warp's R+1 prefixes and R maxima for the merge.
 template <int R>
@@ -448,10 +448,12 @@ __device__ __forceinline__ void tile_scan(const unsigned char* lut_b, const unsi
     int D[R], best[R], PR = 0;
 #pragma unroll
     for (int r = 0; r < R; ++r) D[r] = 0, best[r] = kNeg;
-    // letters of columns (row + d0 + k): wp is 8-byte aligned for R = 8, 4-byte aligned for R = 4
+    // letters of columns (row + d0 + k): wp is aligned to R bytes (8, 4 or 2)
     auto load8 = [](const unsigned char* a) -> uint2 {
         if (R == kR) return *reinterpret_cast<const uint2*>(a);
-        return make_uint2(*reinterpret_cast<const uint32_t*>(a), *reinterpret_cast<const uint32_t*>(a + 4));
+        if (R == 4) return make_uint2(*reinterpret_cast<const uint32_t*>(a), *reinterpret_cast<const uint32_t*>(a + 4));
+        const unsigned short* h = reinterpret_cast<const unsigned short*>(a);
+        return make_uint2((uint32_t)h[0] | ((uint32_t)h[1] << 16), (uint32_t)h[2] | ((uint32_t)h[3] << 16));
     };
     uint2 lw0 = load8(wp);
     for (uint32_t row = 0; row < crow; row += kU) {
@@ -619,10 +621,10 @@ __device__ __forceinline__ void score_body(const KParams& p, const bool epilogue
         // ---- scan: this warp = offset group g, row chunk q
         {
             const uint32_t g = warp & (wd - 1u), q = warp >> wd_log2;
-            if (sd.narrow == 0)
-                tile_scan<kR>(lut_b, win + (g * 32u + lane) * kR + q * crow, s2 + q * crow, crow, csum, cmax, warp, lane);
-            else
-                tile_scan<kR / 2>(lut_b, win + (g * 32u + lane) * (kR / 2) + q * crow, s2 + q * crow, crow, csum, cmax, warp, lane);
+            const unsigned char* wp = win + ((g * 32u + lane) << rl) + q * crow;
+            if (sd.narrow == 0) tile_scan<kR>(lut_b, wp, s2 + q * crow, crow, csum, cmax, warp, lane);
+            else if (sd.narrow == 1) tile_scan<kR / 2>(lut_b, wp, s2 + q * crow, crow, csum, cmax, warp, lane);
+            else tile_scan<kR / 4>(lut_b, wp, s2 + q * crow, crow, csum, cmax, warp, lane);
         }
         __syncthreads();
         if (tl_any && was_first && tid == 0) atomicMax(&times[13], global_ns());
@@ -1526,6 +1528,8 @@ struct sa_session {
     size_t pipe_min_seq = 16384;       // batches at least this large are packed and launched in ranges of >= half of it
                                        // (8192 sequences keep a range above AUTO's threshold for the STREAM kernel)
     uint32_t last_launches = 0;
+    cudaStream_t copy_stream = nullptr;  // pipelined path: range copies run beside the previous range's kernel
+    cudaEvent_t copied[8] = {};
 };
 
 int sa_session_create(int device, sa_session** out) {
@@ -1556,6 +1560,9 @@ void sa_session_destroy(sa_session* s) {
     cudaFree(s->d_blob);
     cudaFree(s->d_out);
     cudaFree(s->d_scratch);
+    for (cudaEvent_t e : s->copied)
+        if (e) cudaEventDestroy(e);
+    if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
 }
@@ -1618,7 +1625,11 @@ int session_solve_pipelined(sa_session* s, const sa_problem* prob, int32_t* out3
     const unsigned nthreads = (unsigned)std::min<size_t>(nranges, std::max(1u, std::min(4u, std::thread::hardware_concurrency() / 2)));
     int rc = session_reserve(s, s->h_in_cap, nseq);  // result table and scratch for the whole batch
     if (rc != SA_OK) return rc;
+    if (!s->copy_stream) SA_CUDA_TRY(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+    for (size_t k = 0; k < nranges; ++k)
+        if (!s->copied[k]) SA_CUDA_TRY(cudaEventCreateWithFlags(&s->copied[k], cudaEventDisableTiming));
     auto rezero = [&]() {
+        cudaStreamSynchronize(s->copy_stream);
         cudaStreamSynchronize(s->stream);
         cudaMemsetAsync(s->d_scratch, 0, sa_cuda_scratch_bytes((uint32_t)s->d_scratch_cap), s->stream);
     };
@@ -1655,7 +1666,10 @@ int session_solve_pipelined(sa_session* s, const sa_problem* prob, int32_t* out3
                 if (r == SA_OK) {
                     std::lock_guard<std::mutex> g(launch_mutex);
                     unsigned char* const d_blob = s->d_blob + k * slot;
-                    const cudaError_t e = cudaMemcpyAsync(d_blob, h_blob, got, cudaMemcpyHostToDevice, s->stream);
+                    // the copy goes to its own stream, so that it runs beside the kernel of an earlier range
+                    cudaError_t e = cudaMemcpyAsync(d_blob, h_blob, got, cudaMemcpyHostToDevice, s->copy_stream);
+                    if (e == cudaSuccess) e = cudaEventRecord(s->copied[k], s->copy_stream);
+                    if (e == cudaSuccess) e = cudaStreamWaitEvent(s->stream, s->copied[k], 0);
                     if (e != cudaSuccess) {
                         r = fail(e, "cudaMemcpyAsync(range)");
                     } else {
@@ -1689,7 +1703,8 @@ int session_solve_pipelined(sa_session* s, const sa_problem* prob, int32_t* out3
         if (need_max.load() != 0) {
             // first large batch of this session (or a larger one than before): grow the buffers — which frees
             // them, so nothing may be in flight — and start over
-            const cudaError_t e = cudaStreamSynchronize(s->stream);
+            cudaError_t e = cudaStreamSynchronize(s->copy_stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
             if (e != cudaSuccess) return fail(e, "cudaStreamSynchronize");
             rc = session_reserve(s, nranges * ((need_max.load() + need_max.load() / 8 + 511) & ~(size_t)255), nseq);
             if (rc != SA_OK) return rc;

@@ -211,7 +211,7 @@ typedef struct sa_tile_item {
     uint8_t pad8[3];
     uint32_t pad;
 } sa_tile_item; /* 32 bytes */
-#define SA_MAX_NARROW 1
+#define SA_MAX_NARROW 2
 
 /* STREAM mode: one self-contained record per pair of sequences scored as u16x2 lanes (what
  * sa_tile_item is for TILE mode): a warp needs the item and this record, nothing else. */

@@ -11,6 +11,7 @@
 #include <random>
 #include <sstream>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "seqalign.h"
@@ -71,6 +72,34 @@ static void check_problem(sa_problem* p, bool run_naive) {
     sa_problem_free(q);
 }
 
+// Ranges of one batch packed by several threads at once (what sa_session_solve does for large batches): every
+// range's blob, walked on the CPU, must give exactly the oracle's rows of that range. Under TSan this is the
+// test of the packer's shared thread pool with several jobs open at the same time.
+static void check_concurrent_ranges(const sa_problem* p) {
+    const uint32_t n = (uint32_t)sa_problem_nseq(p);
+    std::vector<int32_t> want((size_t)n * 3);
+    CHECK(sa_solve_cpu_fast(p, want.data(), 0) == SA_OK, "oracle");
+    const uint32_t nranges = 4;
+    std::vector<int> ok(nranges, 0);
+    std::vector<std::thread> th;
+    for (uint32_t k = 0; k < nranges; ++k)
+        th.emplace_back([&, k] {
+            const uint32_t first = n * k / nranges, count = n * (k + 1) / nranges - first;
+            size_t need = 0, got = 0;
+            if (sa_plan_pack_range(p, first, count, 1, SA_MODE_AUTO, nullptr, 0, &need) != SA_OK) return;
+            std::vector<unsigned char> blob(need);
+            if (sa_plan_pack_range(p, first, count, 1, SA_MODE_AUTO, blob.data(), need, &got) != SA_OK || got != need) return;
+            std::vector<int32_t> out((size_t)count * 4 + 4);
+            if (sa_blob_execute_cpu(blob.data(), got, out.data()) != SA_OK) return;
+            for (uint32_t i = 0; i < count; ++i)
+                for (int c = 0; c < 3; ++c)
+                    if (out[(size_t)i * 4 + c] != want[(size_t)(first + i) * 3 + c]) return;
+            ok[k] = 1;
+        });
+    for (auto& t : th) t.join();
+    for (uint32_t k = 0; k < nranges; ++k) CHECK(ok[k] == 1, "concurrently packed range differs from the oracle");
+}
+
 int main(int argc, char** argv) {
     for (int i = 1; i < argc; ++i) {
         const std::string text = slurp(argv[i]);
@@ -115,6 +144,7 @@ int main(int argc, char** argv) {
         CHECK(sa_problem_create(w, s1.data(), s1.size(), nseq, ptr.data(), len.data(), &p) == SA_OK, "create");
         if (p) {
             check_problem(p, rep < 3);
+            if (rep == 5) check_concurrent_ranges(p);
             sa_problem_free(p);
         }
     }
