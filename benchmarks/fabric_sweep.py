@@ -24,8 +24,11 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--max-bytes", type=int, default=1 << 30)
 ap.add_argument("--iters", type=int, default=7)
 ap.add_argument("--out", default=None)
+ap.add_argument("--only", default="", help="comma-separated subset of: bcast,pull,nccl,argmax (default: all)")
 a = ap.parse_args()
 
+only = set(filter(None, a.only.split(",")))
+want = lambda name: not only or name in only  # noqa: E731
 real = os.dup(1)
 os.dup2(2, 1)
 rank, world, local = init_distributed("nccl")
@@ -74,7 +77,7 @@ while size <= a.max_bytes:
         region.zero_()
     torch.cuda.synchronize()
     dist.barrier()
-    for mc in ([True, False] if fab.mc_ptr else [False]):
+    for mc in (([True, False] if fab.mc_ptr else [False]) if want("bcast") else []):
         fab.use_multicast = mc and world > 1
         fab._desc.use_multicast = 1 if fab.use_multicast else 0
         if rank != 0:
@@ -84,9 +87,22 @@ while size <= a.max_bytes:
         ok = torch.tensor([int(torch.equal(region, expect))], device=dev)
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         emit("bcast", "in-kernel " + ("multimem.st (NVLS)" if mc else "P2P stores"), size, best, med, bool(ok.item()))
+    if want("pull"):
+        if rank != 0:
+            region.zero_()
+        best, med = timed(lambda: fab.pull(size))  # the barrier + all-reduce in timed() put rank 0's bytes in place first
+        expect = torch.arange(size, device=dev, dtype=torch.int64).mul_(2654435761).bitwise_and_(0xFF).to(torch.uint8)
+        ok = torch.tensor([int(torch.equal(region, expect))], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        emit("bcast", "in-kernel pull (LDG over NVLink, every rank its own copy)", size, best, med, bool(ok.item()))
     t = torch.empty(size, dtype=torch.uint8, device=dev)
-    best, med = timed(lambda: dist.broadcast(t, 0))
-    emit("bcast", "NCCL broadcast", size, best, med)
+    if want("nccl"):
+        best, med = timed(lambda: dist.broadcast(t, 0))
+        emit("bcast", "NCCL broadcast", size, best, med)
+    if not want("argmax"):
+        del t
+        size *= 4
+        continue
     # ---------------- argmax reduce (packed u64 keys)
     n = size // 8
     g = torch.Generator(device=dev)

@@ -4,6 +4,9 @@
 //   * broadcast: rank 0 pushes a byte range into every peer's symmetric buffer (NVLS multimem.st
 //     or per-peer P2P stores), chunk by chunk, each chunk followed by a system-scope release
 //     flag; the other ranks' kernels return when every chunk flag has arrived.
+//   * pull: every rank other than 0 copies a byte range OUT OF rank 0's buffer into its own (LDG.128 over
+//     NVLink, STG.128 local) — the data movement the solver uses since round 2; no flags, the range is
+//     resident at rank 0 before anybody launches.
 //   * argmax reduce: every rank folds its packed 64-bit (score, ~index) keys into rank 0's array
 //     with system-scope atomicMax over NVLink, then bumps rank 0's arrival counter; rank 0's
 //     kernel returns when all ranks have arrived.
@@ -72,6 +75,18 @@ __global__ void __launch_bounds__(kThreads) bcast_kernel(const BParams p) {
             }
         }
     }
+}
+
+__global__ void __launch_bounds__(kThreads) pull_kernel(const BParams p) {
+    const int4* const src = reinterpret_cast<const int4*>(p.peer[0] + p.off_blob);
+    int4* const dst = reinterpret_cast<int4*>(p.peer[p.rank] + p.off_blob);
+    const unsigned long long n16 = (p.bytes + 15ull) >> 4, stride = (unsigned long long)gridDim.x * kThreads;
+    unsigned long long i = (unsigned long long)blockIdx.x * kThreads + threadIdx.x;
+    for (; i + 3 * stride < n16; i += 4 * stride) {  // four loads in flight per thread
+        const int4 a = src[i], b = src[i + stride], c = src[i + 2 * stride], d = src[i + 3 * stride];
+        dst[i] = a, dst[i + stride] = b, dst[i + 2 * stride] = c, dst[i + 3 * stride] = d;
+    }
+    for (; i < n16; i += stride) dst[i] = src[i];
 }
 
 __global__ void __launch_bounds__(kThreads) argmax_kernel(const BParams p) {
@@ -152,6 +167,23 @@ int sa_cuda_fabric_bcast(const sa_fabric_desc* f, uint64_t bytes, int ctas, void
     if (grid > p.nchunks) grid = p.nchunks;
     bcast_kernel<<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
     return check_launch("sa_cuda_fabric_bcast");
+}
+
+int sa_cuda_fabric_pull(const sa_fabric_desc* f, uint64_t bytes, int ctas, void* stream) {
+    BParams p{};
+    int rc = fill(f, &p);
+    if (rc != SA_OK) return rc;
+    if (bytes == 0 || bytes > f->layout.max_blob_bytes) {
+        sa_set_last_error("sa_cuda_fabric_pull: size outside the fabric's blob region");
+        return SA_ERR_TOO_LARGE;
+    }
+    if (f->rank == 0) return SA_OK;  // the source has nothing to do
+    p.bytes = bytes;
+    uint32_t grid = ctas > 0 ? (uint32_t)ctas : 296u;
+    const uint64_t need = ((bytes + 15) / 16 + kThreads - 1) / kThreads;
+    if (grid > need) grid = (uint32_t)need;
+    pull_kernel<<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+    return check_launch("sa_cuda_fabric_pull");
 }
 
 int sa_cuda_fabric_argmax(const sa_fabric_desc* f, const void* d_keys, uint64_t nkeys, int ctas, void* stream) {

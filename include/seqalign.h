@@ -389,10 +389,13 @@ int sa_cuda_fabric_solve(const sa_fabric_desc* f, const sa_blob_header* header, 
 /* The two fabric primitives in isolation, for the 1 KB - 1 GB sweep against NCCL and the MPI path
  * (BASELINE.json configs[4]). Both use the same symmetric buffer, flags and epoch discipline as
  * sa_cuda_fabric_solve; every rank calls them once per operation.
- *  bcast : rank 0's blob region [0, bytes) is replicated into every peer's blob region.
+ *  bcast : rank 0's blob region [0, bytes) is replicated into every peer's blob region (rank 0 pushes).
+ *  pull  : the same result, every other rank copying the range out of rank 0's buffer itself (what the
+ *          solver does since blob version 3); the caller makes sure rank 0's range is in place first.
  *  argmax: every rank's nkeys packed u64 keys are max-folded into rank 0's blob region (which rank 0
  *          zeroes beforehand); rank 0's launch ends when all ranks have arrived. */
 int sa_cuda_fabric_bcast(const sa_fabric_desc* f, uint64_t bytes, int ctas, void* stream);
+int sa_cuda_fabric_pull(const sa_fabric_desc* f, uint64_t bytes, int ctas, void* stream);
 int sa_cuda_fabric_argmax(const sa_fabric_desc* f, const void* d_keys, uint64_t nkeys, int ctas, void* stream);
 
 /* One worker of a native multi-process solve (`final --gpus N`; the reference's `mpiexec -np N ./final`,

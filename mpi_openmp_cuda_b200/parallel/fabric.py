@@ -133,6 +133,12 @@ class Fabric:
         stream = torch.cuda.current_stream(self.device).cuda_stream
         N.check(self.lib.sa_cuda_fabric_bcast(C.byref(self._desc), int(nbytes), int(ctas), C.c_void_p(stream)))
 
+    def pull(self, nbytes: int, ctas: int = 0) -> None:
+        """Every rank but 0 copies rank 0's blob region [0, nbytes) into its own (collective; rank 0's bytes must be in place)."""
+        self.lib.sa_cuda_fabric_pull.argtypes = [C.POINTER(FabricDesc), C.c_uint64, C.c_int, C.c_void_p]
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        N.check(self.lib.sa_cuda_fabric_pull(C.byref(self._desc), int(nbytes), int(ctas), C.c_void_p(stream)))
+
     def argmax(self, keys: torch.Tensor, ctas: int = 0) -> None:
         """Max-fold this rank's packed u64 keys (int64 tensor, non-negative) into rank 0's blob region."""
         self.lib.sa_cuda_fabric_argmax.argtypes = [C.POINTER(FabricDesc), C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
