@@ -973,8 +973,10 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
     if (!kFabric && hdr->magic != SA_BLOB_MAGIC) return;  // never walk memory that is not a packed problem
     const uint32_t seq1_bytes = (hdr->len1_padded + 15u) & ~15u;
     uint32_t* const lutlo = reinterpret_cast<uint32_t*>(smem);
-    uint32_t* const luthi = lutlo + SA_ALPHABET * SA_ALPHABET;
-    unsigned char* const seq1s = reinterpret_cast<unsigned char*>(luthi + SA_ALPHABET * SA_ALPHABET);
+    // lutd[code][l] = the biased values of letters 2*(l & 15) and 2*(l & 15) + 1 as two 16-bit halves; each row holds
+    // them twice (l = 0..15 and 16..31), so that the two half-warps of the profile build below read different banks
+    uint32_t* const lutd = lutlo + SA_ALPHABET * SA_ALPHABET;
+    unsigned char* const seq1s = reinterpret_cast<unsigned char*>(lutd + SA_ALPHABET * SA_ALPHABET);
     uint32_t* const prof = reinterpret_cast<uint32_t*>(seq1s + seq1_bytes);
     unsigned long long* const mbar = reinterpret_cast<unsigned long long*>(prof + kWarps * SA_STREAM_ROW_BLOCK * SA_ALPHABET);
 
@@ -1038,11 +1040,13 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
         bulk_g2s(smem_u32(seq1s), p.blob + hdr->off_seq1, seq1_bytes, bar);
     }
     mbar_wait(bar, 0u);
-    // biased table twice: low half for the first sequence of a pair, high half for the second
+    // biased table (first-k rescan) and its letter-paired form (profile build)
+    for (uint32_t i = tid; i < SA_ALPHABET * SA_ALPHABET; i += kThreads)
+        lutlo[i] = (uint32_t)(reinterpret_cast<const int*>(lutlo)[i] - vmin);
+    __syncthreads();
     for (uint32_t i = tid; i < SA_ALPHABET * SA_ALPHABET; i += kThreads) {
-        const uint32_t v = (uint32_t)(reinterpret_cast<const int*>(lutlo)[i] - vmin);
-        lutlo[i] = v;
-        luthi[i] = v << 16;
+        const uint32_t row = i & ~(SA_ALPHABET - 1u), c = 2u * (i & 15u);
+        lutd[i] = lutlo[row + c] | (lutlo[row + c + 1u] << 16);
     }
     __syncthreads();  // the last block-wide barrier of this kernel
 
@@ -1112,9 +1116,9 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
         const unsigned char* wp = seq1s + n0 + d0;
         uint2 lw0 = *reinterpret_cast<const uint2*>(wp);
         for (uint32_t rb = 0; rb < rows; rb += SA_STREAM_ROW_BLOCK) {
-            // ---- private profile block: row u, lane = letter. Every lane fetches the block's 32+32
-            // codes itself (4 broadcast LDG.128 served by L1) and picks row u's bytes with ALU ops:
-            // the load/store pipe is the busiest unit of this kernel, so no SHFL here.
+            // ---- private profile block. Every lane fetches the block's 32+32 codes itself (4 broadcast
+            // LDG.128 served by L1) and picks its row's bytes with ALU ops: the load/store pipe is the
+            // busiest unit of this kernel (93 % of its wavefront peak under ncu), so no SHFL here.
             uint32_t wa[8], wb[8];
             {
                 const uint4 a0 = *reinterpret_cast<const uint4*>(gA + rb), a1 = *reinterpret_cast<const uint4*>(gA + rb + 16);
@@ -1127,11 +1131,21 @@ __device__ __forceinline__ void stream_body(const KParams& p, const bool epilogu
                     for (int k = 0; k < 8; ++k) wb[k] = 0u;
                 }
             }
+            // Two rows per step: half-warp h builds row 2j + h, a lane the letters 2c and 2c + 1 of it (c = lane & 15):
+            // one LDS per sequence (a wavefront each: the halves read different banks) and one 8-byte store,
+            // 64 wavefronts per block where a row-per-step build needs 96.
+            {
+                const uint32_t h = lane >> 4;
+                const uint32_t sel0 = 0x4440u | h, sel1 = 0x4440u | (2u + h);  // byte (2j + h) & 3 of word j >> 1
+                uint2* const pw2 = reinterpret_cast<uint2*>(pw);
 #pragma unroll
-            for (int u = 0; u < (int)SA_STREAM_ROW_BLOCK; ++u) {
-                const uint32_t a = __byte_perm(wa[u >> 2], 0u, 0x4440u | (uint32_t)(u & 3)) * SA_ALPHABET + lane;  // code*32 + my letter
-                const uint32_t b = __byte_perm(wb[u >> 2], 0u, 0x4440u | (uint32_t)(u & 3)) * SA_ALPHABET + lane;
-                pw[u * SA_ALPHABET + lane] = lutlo[a] | luthi[b];
+                for (int j = 0; j < (int)SA_STREAM_ROW_BLOCK / 2; ++j) {
+                    const uint32_t sel = (j & 1) ? sel1 : sel0;
+                    const uint32_t va = lutd[__byte_perm(wa[j >> 1], 0u, sel) * SA_ALPHABET + lane];
+                    const uint32_t vb = lutd[__byte_perm(wb[j >> 1], 0u, sel) * SA_ALPHABET + lane];
+                    // row 2j + h, words 2c and 2c + 1 = 8-byte slot (2j + h) * 16 + c = 32 j + lane
+                    pw2[j * 32 + lane] = make_uint2(__byte_perm(va, vb, 0x5410u), __byte_perm(va, vb, 0x7632u));
+                }
             }
             __syncwarp();
             // ---- scan the block: 4 trips of 8 rows
