@@ -37,7 +37,7 @@ struct Alphabet {
     bool ok = true;
 };
 Alphabet build_alphabet(const sa_problem& p);
-Alphabet letters_only_alphabet();  // A-Z only; every other byte maps to a negative code
+const Alphabet& letters_only_alphabet();  // A-Z only; every other byte maps to a negative code
 
 // value(seq2 code a, seq1 code b) laid out lut[a*32+b]; pad code scores 0.
 void build_lut(const Alphabet& al, const int32_t w[4], int32_t lut[SA_ALPHABET * SA_ALPHABET]);

@@ -670,7 +670,17 @@ int sa_plan_pack_range(const sa_problem* p, uint32_t first, uint32_t count, int 
     for (int attempt = 0; attempt < 2; ++attempt) {
         std::atomic<int> unknown_byte{0};
         build_lut(al, p->weights, reinterpret_cast<int32_t*>(base + off_lut));
-        {
+        if (attempt == 0) {  // letters only: code = low five bits, stored pre-scaled by 4 (a vectorised pass)
+            const unsigned char* __restrict src = reinterpret_cast<const unsigned char*>(p->seq1.data());
+            unsigned char* __restrict d1 = base + off_seq1;
+            unsigned char notletter = 0;
+            for (uint32_t j = 0; j < len1; ++j) {
+                const unsigned char c = src[j];
+                d1[j] = (unsigned char)((c & 31u) << 2);
+                notletter |= (unsigned char)((unsigned char)(c - 'A') > 25u);
+            }
+            if (notletter) unknown_byte.store(1);
+        } else {
             int bad = 0;
             for (uint32_t j = 0; j < len1; ++j) {
                 const int c = al.code[(unsigned char)p->seq1[j]];
