@@ -21,6 +21,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <climits>
 #include <cstdint>
 #include <cstdio>
@@ -64,6 +65,8 @@ struct KParams {
     unsigned long long timeout_ns;
     uint32_t timeline;  // 1: record the globaltimer timeline in the control block
     uint32_t skip_push; // 1: re-solve of the blob every rank already holds (resident re-solve)
+    uint32_t* done_flag;  // single-GPU launches: pinned host word that receives done_epoch once every result row is visible
+    uint32_t done_epoch;  // to the host (the session waits on it instead of on the stream: several microseconds sooner)
     uint32_t dbg_src;   // debug (SA_DEBUG_SRC): bit 0 read Seq2 letters, bit 1 read items/records from rank 0's copy instead of the staged one
 };
 
@@ -425,14 +428,21 @@ __device__ __forceinline__ void launch_epilogue(const KParams& p) {
         }
     }
     if (tid == 0) {
-        __threadfence();
+        const bool tell_host = !kFabric && p.done_flag != nullptr;
+        // result rows written by this CTA sit in pinned host memory: with a host that polls the flag below
+        // instead of waiting for the launch to end, they must be visible system-wide before the count
+        if (tell_host) __threadfence_system(); else __threadfence();
         const unsigned int done = atomicAdd(&my_ctl[kCtlCtasDone], 1u);
+        if (p.timeline) atomicMax(&times[16], global_ns());
         if (done + 1u == gridDim.x) {
             my_ctl[kCtlNext] = 0u;
             my_ctl[kCtlCtasDone] = 0u;
             my_ctl[kCtlSharedNext] = 0u;
+            if (tell_host) {  // the last store of the launch
+                __threadfence_system();
+                st_relaxed_sys(p.done_flag, p.done_epoch);
+            }
         }
-        if (p.timeline) atomicMax(&times[16], global_ns());
     }
 }
 
@@ -1353,7 +1363,19 @@ int sa_cuda_scratch_init(void* d_scratch, size_t bytes, void* stream) {
     return SA_OK;
 }
 
+namespace {
+int solve_blob_impl(const void* d_blob, const sa_blob_header* h, int32_t* d_out, void* d_scratch, void* stream, uint32_t* done_flag,
+                    uint32_t done_epoch);
+}
+
 int sa_cuda_solve_blob(const void* d_blob, const sa_blob_header* h, int32_t* d_out, void* d_scratch, void* stream) {
+    return solve_blob_impl(d_blob, h, d_out, d_scratch, stream, nullptr, 0u);
+}
+
+namespace {
+// done_flag: see KParams (TILE and STREAM launches only; the PAIR kernel ignores it, so callers pass none there)
+int solve_blob_impl(const void* d_blob, const sa_blob_header* h, int32_t* d_out, void* d_scratch, void* stream, uint32_t* done_flag,
+                    uint32_t done_epoch) {
     if (!d_blob || !h || !d_out || !d_scratch) {
         sa_set_last_error("sa_cuda_solve_blob: null argument");
         return SA_ERR_ARG;
@@ -1389,6 +1411,8 @@ int sa_cuda_solve_blob(const void* d_blob, const sa_blob_header* h, int32_t* d_o
     p.write_empty = 1;
     static const bool env_timeline = std::getenv("SA_TIMELINE") != nullptr;  // debug: phase timestamps in the control words
     p.timeline = env_timeline ? 1u : 0u;
+    p.done_flag = done_flag;
+    p.done_epoch = done_epoch;
     if (h->flags & SA_FLAG_STREAM_MODE) {
         const uint32_t smem = 2u * kLutBytes + ((h->len1_padded + 15u) & ~15u) +
                               (uint32_t)kWarps * SA_STREAM_ROW_BLOCK * SA_ALPHABET * 4u + 64u;
@@ -1453,6 +1477,7 @@ int sa_cuda_solve_blob(const void* d_blob, const sa_blob_header* h, int32_t* d_o
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return SA_OK;
 }
+}  // namespace
 
 int sa_cuda_solve_problem(const sa_problem* prob, int32_t* out, int device) {
     if (!prob || !out) {
@@ -1542,6 +1567,9 @@ struct sa_session {
     size_t pipe_min_seq = 16384;       // batches at least this large are packed and launched in ranges of >= half of it
                                        // (8192 sequences keep a range above AUTO's threshold for the STREAM kernel)
     uint32_t last_launches = 0;
+    uint32_t* h_flag = nullptr;          // pinned: the kernel's "every row is visible" word (see KParams::done_flag)
+    uint32_t flag_epoch = 0;
+    size_t flag_max_seq = 4096;          // problems up to this size are waited for by polling the flag
     cudaStream_t copy_stream = nullptr;  // pipelined path: range copies run beside the previous range's kernel
     cudaEvent_t copied[8] = {};
 };
@@ -1556,6 +1584,9 @@ int sa_session_create(int device, sa_session** out) {
     if (!s) return SA_ERR_NOMEM;
     s->device = device;
     if (const char* v = std::getenv("SA_PIPE_MIN_SEQ")) s->pipe_min_seq = (size_t)std::atoll(v);  // 0 = never pipeline
+    if (const char* v = std::getenv("SA_FLAG_MAX_SEQ")) s->flag_max_seq = (size_t)std::atoll(v);  // 0 = always wait on the stream
+    if (cudaMallocHost(reinterpret_cast<void**>(&s->h_flag), 64) == cudaSuccess) *s->h_flag = 0u;
+    else s->h_flag = nullptr, cudaGetLastError();
     cudaError_t e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) {
         delete s;
@@ -1571,6 +1602,7 @@ void sa_session_destroy(sa_session* s) {
     if (s->stream) cudaStreamSynchronize(s->stream);
     cudaFreeHost(s->h_in);
     cudaFreeHost(s->h_out);
+    cudaFreeHost(s->h_flag);
     cudaFree(s->d_blob);
     cudaFree(s->d_out);
     cudaFree(s->d_scratch);
@@ -1785,7 +1817,11 @@ int sa_session_solve(sa_session* s, const sa_problem* prob, int32_t* out3) {
     // The scratch is carved by the CURRENT nseq and is only correct while the whole buffer is zero between
     // solves; a launch that did not run to completion leaves dirty words, so any failure re-zeroes it.
     auto rezero = [&]() { cudaMemsetAsync(s->d_scratch, 0, sa_cuda_scratch_bytes((uint32_t)s->d_scratch_cap), s->stream); };
-    rc = sa_cuda_solve_blob(blob_dev, h, out_dev, s->d_scratch, s->stream);
+    // Small problems: the kernel's last CTA tells the host through a pinned word that every row is visible, and
+    // the host polls that word — it sees it several microseconds before cudaStreamSynchronize would return.
+    const bool use_flag = s->direct_out && s->h_flag && nseq <= s->flag_max_seq && !(h->flags & SA_FLAG_PAIR_MODE);
+    const uint32_t epoch = use_flag ? ++s->flag_epoch : 0u;
+    rc = solve_blob_impl(blob_dev, h, out_dev, s->d_scratch, s->stream, use_flag ? s->h_flag : nullptr, epoch);
     if (rc != SA_OK) {
         rezero();
         return rc;
@@ -1797,7 +1833,20 @@ int sa_session_solve(sa_session* s, const sa_problem* prob, int32_t* out3) {
             return fail(e, "cudaMemcpyAsync(results)");
         }
     }
-    {
+    bool seen = false;
+    if (use_flag) {
+        const volatile uint32_t* flag = s->h_flag;
+        const auto t0 = std::chrono::steady_clock::now();
+        for (uint32_t spins = 1; !(seen = (*flag == epoch)); ++spins) {
+            __builtin_ia32_pause();
+            if ((spins & 2047u) == 0u) {  // every few tens of microseconds: did the launch die, or is this taking long?
+                const cudaError_t q = cudaStreamQuery(s->stream);
+                if (q != cudaErrorNotReady) break;  // finished (flag is set by now) or failed: the synchronize below tells
+                if (std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(2)) break;  // not a small problem after all
+            }
+        }
+    }
+    if (!seen) {
         const cudaError_t e = cudaStreamSynchronize(s->stream);
         if (e != cudaSuccess) {
             rezero();
