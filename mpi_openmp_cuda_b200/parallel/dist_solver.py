@@ -19,6 +19,8 @@ class DistributedSolver:
         self.fabric = fabric
         self._pin_in = None
         self._pin_out = None
+        self._pin_err = torch.zeros(1, dtype=torch.int32, pin_memory=True) if torch.cuda.is_available() else None
+        self._err_fresh = False
 
     @property
     def rank(self) -> int:
@@ -50,9 +52,14 @@ class DistributedSolver:
         else:
             f.launch(None)
 
-    def fetch(self, nseq: int, sync: bool = True) -> np.ndarray | None:
+    def fetch(self, nseq: int, sync: bool = True, with_error: bool = False) -> np.ndarray | None:
         """Rank 0: D2H of the result table (after its kernel, which ends only when all ranks delivered)."""
         f = self.fabric
+        # this rank's error word rides along with the results: one synchronisation per solve, not two
+        if with_error and self._pin_err is not None:
+            off = f.layout.off_ctrl + 12
+            self._pin_err.copy_(f.buf[off : off + 4].view(torch.int32), non_blocking=True)
+            self._err_fresh = sync
         if f.rank != 0:
             if sync:
                 torch.cuda.current_stream().synchronize()
@@ -65,7 +72,11 @@ class DistributedSolver:
         return self._pin_out[:nseq, :3].numpy()
 
     def check(self) -> None:
-        err = self.fabric.error_word()
+        if self._err_fresh:  # fetched together with the results of the solve that just ended
+            self._err_fresh = False
+            err = int(self._pin_err[0])
+        else:
+            err = self.fabric.error_word()
         if err:
             raise RuntimeError(f"fabric wait timed out on rank {self.rank} (code {err}): a peer GPU did not deliver")
 
@@ -92,10 +103,10 @@ class DistributedSolver:
 
                 blob = self.pack(Problem.from_parts((1, 1, 1, 1), b"A", []))
             self.launch_packed(blob)
-            res = self.fetch(blob.nseq)
+            res = self.fetch(blob.nseq, with_error=True)
             self.check()
             return fallback if fallback is not None else res.copy()
         self.launch_packed(None)
-        self.fetch(0)
+        self.fetch(0, with_error=True)
         self.check()
         return None
