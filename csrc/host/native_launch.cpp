@@ -178,32 +178,28 @@ int serve_round(const std::vector<int>& socks, int timeout_ms, std::string& why)
     const int world = (int)socks.size();
     std::vector<sa_wire_msg> msgs(world);
     std::vector<int> fds_of(world, -1);
+    auto close_all = [&]() {
+        for (int& fd : fds_of)
+            if (fd >= 0) close(fd), fd = -1;
+    };
     for (int r = 0; r < world; ++r) {
         struct pollfd p = {socks[r], POLLIN, 0};
         const int pr = poll(&p, 1, timeout_ms);
         int fds[SA_WIRE_MAX_FDS];
         if (pr <= 0 || sa_wire_recv(socks[r], &msgs[r], fds) != 0) {
             why = "worker " + std::to_string(r) + (pr == 0 ? " did not answer in time" : " went away");
+            close_all();
             return -1;
         }
-        if (msgs[r].nfds > 1) {
-            why = "worker " + std::to_string(r) + " sent a malformed message";
-            return -1;
-        }
-        if (msgs[r].nfds == 1) fds_of[r] = fds[0];
-        if (msgs[r].type == SA_WIRE_DONE && msgs[r].value != 0) {
-            why = "worker " + std::to_string(r) + " reported an error";
-            return -1;
-        }
-        if (msgs[r].type != msgs[0].type) {
-            why = "workers are out of step";
-            return -1;
-        }
+        for (uint32_t i = 1; i < msgs[r].nfds; ++i) close(fds[i]);  // a worker sends at most one descriptor per round
+        if (msgs[r].nfds >= 1) fds_of[r] = fds[0];
+        if (msgs[r].nfds > 1) why = "worker " + std::to_string(r) + " sent a malformed message";
+        else if (msgs[r].type == SA_WIRE_DONE && msgs[r].value != 0) why = "worker " + std::to_string(r) + " reported an error";
+        else if (msgs[r].type != msgs[0].type) why = "workers are out of step";
+        else continue;
+        close_all();
+        return -1;
     }
-    auto close_all = [&]() {
-        for (int fd : fds_of)
-            if (fd >= 0) close(fd);
-    };
     sa_wire_msg reply = msgs[0];
     int rc = 0;
     switch (msgs[0].type) {
