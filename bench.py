@@ -225,7 +225,7 @@ def run_ours(args):
         "gpu_launches": m["launches"],
         "clocks": m["clocks"],
     }
-    pe = process_e2e(input_bytes(args, n_gpus), n_gpus, runs=int(os.environ.get("SA_BENCH_PROC_RUNS", "3")))
+    pe = process_e2e(input_bytes(args, n_gpus), n_gpus, runs=int(os.environ.get("SA_BENCH_PROC_RUNS", "3" if n_gpus == 1 else "2")))
     if pe is not None and "error" not in pe:
         from mpi_openmp_cuda_b200 import format_results
 
