@@ -49,3 +49,21 @@ def test_score_formula_on_the_reported_candidate(w, seq1, seq2):
         j = i + n if (k == 0 or i < k) else i + n + 1
         total += vals[pair_class(c, seq1[j])]
     assert total == score
+
+
+@settings(max_examples=80, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@given(w=weights, seq1=st.text(alphabet="ABCDEFGHIKLMNPQRSTVWY-", min_size=1, max_size=300), seqs=st.lists(letters, min_size=1, max_size=9),
+       cut=st.tuples(st.integers(min_value=0, max_value=9), st.integers(min_value=0, max_value=9)), split=st.booleans(),
+       world=st.integers(min_value=1, max_value=3))
+def test_ranges_narrow_tiles_and_split_tiles_match_the_oracle(w, seq1, seqs, cut, split, world):
+    """Round-2 planner paths: a range of the sequences packed on its own (what the session does for large
+    batches), the latency mode's narrow tiles (small problems always get them), tiles of one sequence dealt
+    over several ranks. Whatever the cut, row i of a range is sequence first + i of the oracle."""
+    p = Problem.from_parts(w, seq1, seqs)
+    ref = solve_cpu(p, "fast")
+    first = min(cut[0], p.nseq)
+    count = min(cut[1], p.nseq - first)
+    blob = plan.plan_pack_range(p, first, count, mode="tile")
+    assert np.array_equal(plan.execute_blob_cpu(blob), ref[first:first + count])
+    whole = plan.plan_pack(p, world, mode="tile", split_tiles=split)
+    assert np.array_equal(plan.execute_blob_cpu(whole), ref)
