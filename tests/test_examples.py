@@ -22,3 +22,15 @@ def test_cpp_gpu_example_compiles(tmp_path):
         pytest.skip("CUDA library not built")
     subprocess.run(["g++", "-std=c++17", "-Wall", "-Iinclude", "-c", "examples/solve_gpu.cpp", "-o", str(tmp_path / "solve_gpu.o")],
                    cwd=ROOT, check=True)
+
+
+@pytest.mark.parametrize("nranges", [1, 3, 40])
+def test_range_packing_example_reproduces_goldens(tmp_path, shipped_inputs, nranges):
+    """examples/pack_ranges.c: sa_plan_pack_range + the CPU walk, range by range (more ranges than sequences included)."""
+    exe = tmp_path / "pack_ranges"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Iinclude", "examples/pack_ranges.c", f"-L{LIB}", "-lseqalign_core",
+                    f"-Wl,-rpath,{LIB}", "-o", str(exe)], cwd=ROOT, check=True)
+    for i in (1, 3, 6):
+        path, gold = shipped_inputs[i]
+        out = subprocess.run([str(exe), str(nranges)], stdin=open(path, "rb"), capture_output=True, check=True)
+        assert out.stdout == gold.read_bytes()
