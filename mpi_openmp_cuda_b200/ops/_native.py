@@ -122,7 +122,7 @@ def cuda() -> C.CDLL:
     lib.sa_session_create.argtypes = [C.c_int, C.POINTER(vp)]
     lib.sa_session_destroy.argtypes = [vp]
     lib.sa_session_destroy.restype = None
-    lib.sa_session_solve.argtypes = [vp, vp, C.POINTER(C.c_int32)]
+    lib.sa_session_solve.argtypes = [vp, vp, vp]  # the result pointer is passed as an address (see NativeSession.solve)
     lib.sa_session_configure.argtypes = [vp, C.c_size_t, C.c_int]
     lib.sa_session_configure.restype = None
     lib.sa_session_last_bytes.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]

@@ -58,7 +58,10 @@ class Problem:
 
     @property
     def nseq(self) -> int:
-        return int(N.core().sa_problem_nseq(self._h))
+        n = getattr(self, "_nseq", None)  # a parsed problem never changes: ask the library once
+        if n is None:
+            n = self._nseq = int(N.core().sa_problem_nseq(self._h))
+        return n
 
     @property
     def weights(self) -> tuple[int, int, int, int]:
