@@ -236,14 +236,14 @@ int sa_plan_pack_range(const sa_problem* p, uint32_t first, uint32_t count, int 
     const uint32_t len1 = (uint32_t)p->seq1.size();
     const uint32_t nseq = count;
     const std::string* const seq2 = p->seq2.data() + first;
-    // SA_PACK_TIMING=1: phase times of this call on stderr (profiling aid; see benchmarks/pack_phases.py)
+    // SA_PACK_TIMING=1: phase times of this call on stderr (profiling aid; the printing itself is not counted)
     static const bool timing = std::getenv("SA_PACK_TIMING") != nullptr;
     auto t_prev = std::chrono::steady_clock::now();
     auto mark = [&](const char* what) {
         if (!timing || !dst) return;
         const auto t = std::chrono::steady_clock::now();
         std::fprintf(stderr, "pack %-10s %8.1f us\n", what, std::chrono::duration<double, std::micro>(t - t_prev).count());
-        t_prev = t;
+        t_prev = std::chrono::steady_clock::now();
     };
     if (p->seq1.size() > SA_GPU_MAX_SEQ1) {
         set_error("Seq1 longer than the GPU executor supports");
