@@ -510,7 +510,13 @@ int sa_plan_pack_range(const sa_problem* p, uint32_t first, uint32_t count, int 
         // costliest first; PAIR geometries differ per pair and need the sort
         if (!use_stream)
             std::stable_sort(pairs.begin(), pairs.end(), [](const Pair& x, const Pair& y) { return x.g.item_cost > y.g.item_cost; });
-        if (use_stream) {
+        if (use_stream && world == 1) {
+            rank_first_pair[0] = 0;
+            for (size_t r = 1; r <= SA_MAX_WORLD; ++r) rank_first_pair[r] = (uint32_t)pairs.size();
+            per_rank[0].reserve(nitems);
+            for (uint32_t pid = 0; pid < pairs.size(); ++pid)
+                for (uint32_t t = 0; t < pairs[pid].g.ntiles; ++t) per_rank[0].push_back({pid, t});
+        } else if (use_stream) {
             // whole pairs are dealt to the least-loaded rank, costliest first: every atomic stays local
             std::vector<uint64_t> load((size_t)world, 0);
             std::vector<uint8_t> pair_rank(pairs.size(), 0);
@@ -598,7 +604,18 @@ int sa_plan_pack_range(const sa_problem* p, uint32_t first, uint32_t count, int 
     std::vector<std::vector<uint32_t>> group((size_t)world);
     {
         std::vector<uint8_t> placed(nseq, 0);
-        for (int r = 0; r < world; ++r)
+        for (int r = 0; r < world; ++r) group[(size_t)r].reserve(by_tile ? (r == 0 ? nseq : 0u) : nseq / (uint32_t)world + 16u);
+        if (use_stream) {
+            // a rank's items are its pairs in order, all tiles of a pair in a row: first-seen order = pair order
+            for (int r = 0; r < world; ++r)
+                for (uint32_t pid = rank_first_pair[(size_t)r]; pid < rank_first_pair[(size_t)r + 1]; ++pid)
+                    for (uint32_t s : {pairs[pid].a, pairs[pid].b}) {
+                        if (s == SA_NO_SEQ || placed[s]) continue;
+                        placed[s] = 1;
+                        group[(size_t)home[s]].push_back(s);
+                    }
+        }
+        for (int r = 0; r < world && !use_stream; ++r)
             for (const RankItem& it : per_rank[(size_t)r]) {
                 uint32_t members[2] = {it.seq, SA_NO_SEQ};
                 if (use_stream) members[0] = pairs[it.seq].a, members[1] = pairs[it.seq].b;
